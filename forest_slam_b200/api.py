@@ -1,0 +1,594 @@
+"""Host-side mirror of the call expressions the reference's frame loop makes.
+
+Two layers:
+
+* batched operators (``*_batch``) taking CUDA ``torch.Tensor`` frame banks / correspondence batches and
+  returning CUDA tensors — the form the sequence and loop-closure drivers use;
+* cv2-shaped single-pair functions (``BFMatcher``, ``findEssentialMat``, ``recoverPose``,
+  ``solvePnPRansac``, ``Rodrigues`` …) taking and returning NumPy arrays exactly like the calls in
+  ``ros_ws/src/mono_slam.py:106-112`` and ``ros_ws/src/stereo_slam.py:85,234,264-298``, so that the
+  reference scripts can swap ``cv2.`` for ``fsb.`` on those lines.
+
+Everything runs in the CUDA extension through the C ABI (include/forestslam_b200.h); PyTorch only owns
+device memory and streams.  There is no CPU path in this module.
+"""
+from __future__ import annotations
+
+import collections
+import ctypes as C
+import dataclasses
+import math
+from typing import Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FSCamera
+
+NORM_HAMMING = 6  # cv2.NORM_HAMMING
+NORM_L2 = 4       # cv2.NORM_L2
+RANSAC = 8        # cv2.RANSAC
+SOLVEPNP_ITERATIVE = 0
+
+DMatch = collections.namedtuple("DMatch", ["queryIdx", "trainIdx", "distance"])
+
+
+# ------------------------------------------------------------------------------------------- constants
+@dataclasses.dataclass(frozen=True)
+class ForestCamera:
+    """Intrinsics / distortion / baseline of the BotanicGarden rig (stereo_slam.py:45-64, mono_slam.py:40-50)."""
+    fx: float = 642.9165664800531
+    fy: float = 641.9171825800378
+    cx: float = 460.1840658156501
+    cy: float = 308.5846449100310
+    dist: Tuple[float, ...] = (-0.060164620903866, 0.094005180631043, 0.0, 0.0, 0.0)
+    baseline: float = 0.253736175410149  # np.linalg.norm(T_rgb0_rgb1[:3, 3]) of the 1x16 array, stereo_slam.py:270
+    width: int = 960
+    height: int = 600
+
+    @property
+    def K(self) -> np.ndarray:
+        return np.array([[self.fx, 0.0, self.cx], [0.0, self.fy, self.cy], [0.0, 0.0, 1.0]])
+
+    def as_struct(self) -> FSCamera:
+        s = FSCamera()
+        s.fx, s.fy, s.cx, s.cy = self.fx, self.fy, self.cx, self.cy
+        d = list(self.dist) + [0.0] * (5 - len(self.dist))
+        for i in range(5):
+            s.dist[i] = float(d[i])
+        return s
+
+
+def camera_from_K(K, dist=None) -> ForestCamera:
+    K = np.asarray(K, dtype=np.float64)
+    d = np.zeros(5) if dist is None else np.asarray(dist, dtype=np.float64).reshape(-1)
+    d = np.concatenate([d, np.zeros(max(0, 5 - d.size))])[:5]
+    return ForestCamera(fx=float(K[0, 0]), fy=float(K[1, 1]), cx=float(K[0, 2]), cy=float(K[1, 2]),
+                        dist=tuple(float(x) for x in d))
+
+
+# ------------------------------------------------------------------------------------------- plumbing
+def _dev(device=None) -> torch.device:
+    if not torch.cuda.is_available():
+        raise _lib.ForestSlamError("a CUDA device is required: forest_slam_b200 has no CPU fallback")
+    return torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+_workspaces = {}
+
+
+def _workspace(nbytes: int, device: torch.device, slot: str = "default") -> torch.Tensor:
+    key = (device.index, slot)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _chk(t: torch.Tensor, dtype, name: str) -> torch.Tensor:
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise TypeError(f"{name} must be a CUDA torch.Tensor")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    return t.contiguous()
+
+
+def _to_cuda(a, dtype, device) -> torch.Tensor:
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype, non_blocking=True).contiguous()
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device=device, dtype=dtype, non_blocking=True)
+
+
+def _pairs(pair_a, pair_b, device):
+    a = _to_cuda(pair_a, torch.int32, device)
+    b = _to_cuda(pair_b, torch.int32, device)
+    if a.shape != b.shape or a.dim() != 1:
+        raise ValueError("pair_a / pair_b must be 1-D and of equal length")
+    return a, b
+
+
+# ------------------------------------------------------------------------------------------- A2
+def hamming_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, *, cross_check: bool = True,
+                        ratio: Optional[float] = None, want_matches1: bool = True):
+    """Batched cv2.BFMatcher(NORM_HAMMING, crossCheck).match over a frame bank (stereo_slam.py:85,234,242).
+
+    desc [F, n_max, 32] uint8, counts [F] int32 → dict(matches0, dist0, second0, matches1, n_matches)."""
+    lib = _lib.load()
+    desc = _chk(desc, torch.uint8, "desc")
+    if desc.dim() != 3 or desc.shape[2] != 32:
+        raise ValueError("desc must be [n_frames, n_max, 32] uint8")
+    dev = desc.device
+    F, n_max = int(desc.shape[0]), int(desc.shape[1])
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    a, b = _pairs(pair_a, pair_b, dev)
+    P = int(a.numel())
+    m0 = torch.empty((P, n_max), dtype=torch.int32, device=dev)
+    d0 = torch.empty_like(m0)
+    s0 = torch.empty_like(m0)
+    m1 = torch.empty_like(m0) if want_matches1 else None
+    nm = torch.empty((P,), dtype=torch.int32, device=dev)
+    nbytes = lib.fs_hamming_match_workspace_bytes(P, n_max)
+    ws = _workspace(nbytes, dev)
+    _lib.check(lib.fs_hamming_match(_p(desc), F, n_max, _p(counts), _p(a), _p(b), P, int(bool(cross_check)),
+                                    float(ratio) if ratio else 0.0, _p(m0), _p(d0), _p(s0), _p(m1), _p(nm),
+                                    _p(ws), ws.numel(), _stream()), "fs_hamming_match")
+    return {"matches0": m0, "dist0": d0, "second0": s0, "matches1": m1, "n_matches": nm}
+
+
+# ------------------------------------------------------------------------------------------- A1
+def float_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
+    """[F, 256, n_max] fp32 channel-major (SuperPoint layout) → [F, n_max, 512] split-bf16 operand bank."""
+    lib = _lib.load()
+    desc = _chk(desc, torch.float32, "desc")
+    if desc.dim() != 3 or desc.shape[1] != 256:
+        raise ValueError("desc must be [n_frames, 256, n_max] float32")
+    dev = desc.device
+    F, n_max = int(desc.shape[0]), int(desc.shape[2])
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    ops = torch.empty((F, n_max, 512), dtype=torch.bfloat16, device=dev)
+    _lib.check(lib.fs_float_prepare(_p(desc), F, n_max, _p(counts), _p(ops), _stream()), "fs_float_prepare")
+    return ops
+
+
+def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, *, scale: float = 1.0,
+                      threshold: Optional[float] = None, ratio: Optional[float] = None,
+                      operands: Optional[torch.Tensor] = None, exact_fp32: bool = False):
+    """Batched float-descriptor mutual-NN (+threshold, +ratio): superglue.py:259-260, :268-278.
+
+    desc [F, 256, n_max] fp32.  The tensor-core path (default when n_max % 128 == 0) reads the split-bf16
+    operand bank (``operands`` or prepared on the fly); ``exact_fp32`` selects the CUDA-core fp32 kernel."""
+    lib = _lib.load()
+    if desc is not None:
+        desc = _chk(desc, torch.float32, "desc")
+        dev = desc.device
+        F, n_max = int(desc.shape[0]), int(desc.shape[2])
+    else:
+        if operands is None:
+            raise ValueError("either desc or operands is required")
+        dev = operands.device
+        F, n_max = int(operands.shape[0]), int(operands.shape[1])
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    a, b = _pairs(pair_a, pair_b, dev)
+    P = int(a.numel())
+    m0 = torch.empty((P, n_max), dtype=torch.int32, device=dev)
+    m1 = torch.empty_like(m0)
+    sc = torch.empty((P, n_max), dtype=torch.float32, device=dev)
+    se = torch.empty_like(sc)
+    nm = torch.empty((P,), dtype=torch.int32, device=dev)
+    thr = -math.inf if threshold is None else float(threshold)
+    rat = float(ratio) if ratio else 0.0
+    nbytes = lib.fs_float_match_workspace_bytes(P, n_max)
+    ws = _workspace(nbytes, dev)
+    use_tc = (not exact_fp32) and n_max % 128 == 0
+    if use_tc:
+        if operands is None:
+            operands = float_prepare(desc, counts)
+        _lib.check(lib.fs_float_match(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
+                                      rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(ws), ws.numel(),
+                                      _stream()), "fs_float_match")
+    else:
+        if desc is None:
+            raise ValueError("the fp32 kernel needs desc")
+        _lib.check(lib.fs_float_match_fp32(_p(desc), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
+                                           rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(ws), ws.numel(),
+                                           _stream()), "fs_float_match_fp32")
+    return {"matches0": m0, "matches1": m1, "score0": sc, "second0": se, "n_matches": nm}
+
+
+# ------------------------------------------------------------------------------------------- A3
+def gather_matches_batch(kpts: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, matches0: torch.Tensor):
+    """valid = matches > -1; mkpts0 = kpts0[valid]; mkpts1 = kpts1[matches[valid]] (mono_slam.py:106-108)."""
+    lib = _lib.load()
+    kpts = _chk(kpts, torch.float32, "kpts")
+    dev = kpts.device
+    F, n_max = int(kpts.shape[0]), int(kpts.shape[1])
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    a, b = _pairs(pair_a, pair_b, dev)
+    P = int(a.numel())
+    matches0 = _chk(matches0, torch.int32, "matches0")
+    mk0 = torch.zeros((P, n_max, 2), dtype=torch.float32, device=dev)
+    mk1 = torch.zeros_like(mk0)
+    nc = torch.empty((P,), dtype=torch.int32, device=dev)
+    src = torch.empty((P, n_max), dtype=torch.int32, device=dev)
+    _lib.check(lib.fs_gather_matches(_p(kpts), F, n_max, _p(counts), _p(a), _p(b), P, _p(matches0), _p(mk0),
+                                     _p(mk1), _p(nc), _p(src), _stream()), "fs_gather_matches")
+    return {"mkpts0": mk0, "mkpts1": mk1, "n_corr": nc, "src_idx": src}
+
+
+# ------------------------------------------------------------------------------------------- A6
+def backproject_stereo(pts, disparity, *, camera: ForestCamera = ForestCamera(), baseline: Optional[float] = None,
+                       zmin: float = 0.1, zmax: float = 1000.0, map_index=None):
+    """depth = fx*B/disp; Z = depth[int(y), int(x)]; X, Y pin-hole; gate (stereo_slam.py:264-289).
+
+    pts [n, 2] f32; disparity [n] (per point) or [H, W] / [M, H, W] dense maps.  → (points3D [n,3], valid [n])."""
+    lib = _lib.load()
+    dev = pts.device if isinstance(pts, torch.Tensor) and pts.is_cuda else _dev()
+    pts_t = _to_cuda(pts, torch.float32, dev).reshape(-1, 2)
+    disp = _to_cuda(disparity, torch.float32, dev)
+    n = int(pts_t.shape[0])
+    if disp.dim() == 1:
+        if disp.numel() != n:
+            raise ValueError("per-point disparity must have one value per point")
+        mh = mw = 0
+    else:
+        if disp.dim() == 2:
+            disp = disp[None]
+        mh, mw = int(disp.shape[1]), int(disp.shape[2])
+    mi = None if map_index is None else _to_cuda(map_index, torch.int32, dev)
+    out = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    valid = torch.empty((n,), dtype=torch.uint8, device=dev)
+    cam = camera.as_struct()
+    B = camera.baseline if baseline is None else float(baseline)
+    _lib.check(lib.fs_backproject_stereo(_p(pts_t), _p(disp), _p(mi), n, mh, mw, C.byref(cam), B, zmin, zmax,
+                                         _p(out), _p(valid), _stream()), "fs_backproject_stereo")
+    return out, valid
+
+
+def backproject_filter_batch(mkpts0, mkpts1, disparity, n_corr, *, camera: ForestCamera = ForestCamera(),
+                             baseline: Optional[float] = None, zmin: float = 0.1, zmax: float = 1000.0):
+    """Batched A6 + the joint filter of stereo_slam.py:288-289 → dict(points3d, pts2d, n_out)."""
+    lib = _lib.load()
+    mkpts0 = _chk(mkpts0, torch.float32, "mkpts0")
+    mkpts1 = _chk(mkpts1, torch.float32, "mkpts1")
+    disparity = _chk(disparity, torch.float32, "disparity")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    dev = mkpts0.device
+    P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
+    p3 = torch.zeros((P, n_max, 3), dtype=torch.float32, device=dev)
+    p2 = torch.zeros((P, n_max, 2), dtype=torch.float32, device=dev)
+    no = torch.empty((P,), dtype=torch.int32, device=dev)
+    cam = camera.as_struct()
+    B = camera.baseline if baseline is None else float(baseline)
+    _lib.check(lib.fs_backproject_filter(_p(mkpts0), _p(mkpts1), _p(disparity), _p(n_corr), P, n_max,
+                                         C.byref(cam), B, zmin, zmax, _p(p3), _p(p2), _p(no), _stream()),
+               "fs_backproject_filter")
+    return {"points3d": p3, "pts2d": p2, "n_out": no}
+
+
+# ------------------------------------------------------------------------------------------- A4 / A5
+def find_essential_batch(mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[float, float], prob: float = 0.999,
+                         threshold: float = 1.0, max_iters: int = 1000):
+    """Batched cv2.findEssentialMat(..., method=RANSAC) (mono_slam.py:111)."""
+    lib = _lib.load()
+    mkpts0 = _chk(mkpts0, torch.float32, "mkpts0")
+    mkpts1 = _chk(mkpts1, torch.float32, "mkpts1")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    dev = mkpts0.device
+    P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
+    E = torch.zeros((P, 3, 3), dtype=torch.float64, device=dev)
+    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
+    ninl = torch.zeros((P,), dtype=torch.int32, device=dev)
+    iters = torch.zeros((P,), dtype=torch.int32, device=dev)
+    status = torch.zeros((P,), dtype=torch.int32, device=dev)
+    nbytes = lib.fs_find_essential_workspace_bytes(P, n_max, max_iters)
+    ws = _workspace(nbytes, dev, "ransac")
+    _lib.check(lib.fs_find_essential_ransac(_p(mkpts0), _p(mkpts1), _p(n_corr), P, n_max, float(focal),
+                                            float(pp[0]), float(pp[1]), float(prob), float(threshold),
+                                            int(max_iters), _p(E), _p(mask), _p(ninl), _p(iters), _p(status),
+                                            _p(ws), ws.numel(), _stream()), "fs_find_essential_ransac")
+    return {"E": E, "mask": mask, "n_inliers": ninl, "iters": iters, "status": status}
+
+
+def recover_pose_batch(E, mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[float, float],
+                       distance_thresh: float = 50.0, status=None):
+    """Batched cv2.recoverPose(E, p0, p1, focal=, pp=) (mono_slam.py:112)."""
+    lib = _lib.load()
+    E = _chk(E, torch.float64, "E")
+    mkpts0 = _chk(mkpts0, torch.float32, "mkpts0")
+    mkpts1 = _chk(mkpts1, torch.float32, "mkpts1")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    dev = mkpts0.device
+    P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
+    R = torch.zeros((P, 3, 3), dtype=torch.float64, device=dev)
+    t = torch.zeros((P, 3), dtype=torch.float64, device=dev)
+    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
+    ng = torch.zeros((P,), dtype=torch.int32, device=dev)
+    _lib.check(lib.fs_recover_pose(_p(E), _p(mkpts0), _p(mkpts1), _p(n_corr), _p(status), P, n_max,
+                                   float(focal), float(pp[0]), float(pp[1]), float(distance_thresh), _p(R),
+                                   _p(t), _p(mask), _p(ng), _stream()), "fs_recover_pose")
+    return {"R": R, "t": t, "mask": mask, "n_good": ng}
+
+
+def ransac_subsets(n_corr, max_iters: int) -> torch.Tensor:
+    """OpenCV's RANSAC sampler (RNG(2^64-1), 5 distinct indices per iteration) → [P, max_iters, 5] int32."""
+    lib = _lib.load()
+    dev = n_corr.device if isinstance(n_corr, torch.Tensor) and n_corr.is_cuda else _dev()
+    n_corr = _to_cuda(n_corr, torch.int32, dev)
+    P = int(n_corr.numel())
+    out = torch.zeros((P, max_iters, 5), dtype=torch.int32, device=dev)
+    _lib.check(lib.fs_ransac_subsets(_p(n_corr), P, int(max_iters), _p(out), _stream()), "fs_ransac_subsets")
+    return out
+
+
+def score_essential_batch(mkpts0, mkpts1, n_corr, models_E, *, focal, pp, threshold: float = 1.0):
+    """Sampson-score [P, H, 3, 3] hypotheses against every correspondence → counts [P, H] (config 4 sweep)."""
+    lib = _lib.load()
+    mkpts0 = _chk(mkpts0, torch.float32, "mkpts0")
+    mkpts1 = _chk(mkpts1, torch.float32, "mkpts1")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    models_E = _chk(models_E, torch.float64, "models_E")
+    P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
+    H = int(models_E.shape[1])
+    counts = torch.zeros((P, H), dtype=torch.int32, device=mkpts0.device)
+    _lib.check(lib.fs_score_essential(_p(mkpts0), _p(mkpts1), _p(n_corr), P, n_max, float(focal), float(pp[0]),
+                                      float(pp[1]), float(threshold), _p(models_E), H, _p(counts), _stream()),
+               "fs_score_essential")
+    return counts
+
+
+def score_pnp_batch(points3d, pts2d, n_corr, models_rt, *, camera: ForestCamera = ForestCamera(),
+                    reproj_error: float = 1.0):
+    """Reprojection-score [P, H, 6] (rvec|tvec) hypotheses → counts [P, H] (config 4 sweep)."""
+    lib = _lib.load()
+    points3d = _chk(points3d, torch.float32, "points3d")
+    pts2d = _chk(pts2d, torch.float32, "pts2d")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    models_rt = _chk(models_rt, torch.float64, "models_rt")
+    P, n_max = int(points3d.shape[0]), int(points3d.shape[1])
+    H = int(models_rt.shape[1])
+    counts = torch.zeros((P, H), dtype=torch.int32, device=points3d.device)
+    cam = camera.as_struct()
+    _lib.check(lib.fs_score_pnp(_p(points3d), _p(pts2d), _p(n_corr), P, n_max, C.byref(cam), float(reproj_error),
+                                _p(models_rt), H, _p(counts), _stream()), "fs_score_pnp")
+    return counts
+
+
+# ------------------------------------------------------------------------------------------- A7
+def solve_pnp_ransac_batch(points3d, pts2d, n_corr, *, camera: ForestCamera = ForestCamera(),
+                           reproj_error: float = 1.0, confidence: float = 0.99, max_iters: int = 1000,
+                           min_points: int = 6):
+    """Batched cv2.solvePnPRansac(..., SOLVEPNP_ITERATIVE) with the >= 6 gate of stereo_slam.py:292-295."""
+    lib = _lib.load()
+    points3d = _chk(points3d, torch.float32, "points3d")
+    pts2d = _chk(pts2d, torch.float32, "pts2d")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    dev = points3d.device
+    P, n_max = int(points3d.shape[0]), int(points3d.shape[1])
+    rvec = torch.zeros((P, 3), dtype=torch.float64, device=dev)
+    tvec = torch.zeros((P, 3), dtype=torch.float64, device=dev)
+    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
+    idx = torch.zeros((P, n_max), dtype=torch.int32, device=dev)
+    ninl = torch.zeros((P,), dtype=torch.int32, device=dev)
+    iters = torch.zeros((P,), dtype=torch.int32, device=dev)
+    status = torch.zeros((P,), dtype=torch.int32, device=dev)
+    cam = camera.as_struct()
+    nbytes = lib.fs_solve_pnp_workspace_bytes(P, n_max, max_iters)
+    ws = _workspace(nbytes, dev, "ransac")
+    _lib.check(lib.fs_solve_pnp_ransac(_p(points3d), _p(pts2d), _p(n_corr), P, n_max, C.byref(cam),
+                                       float(reproj_error), float(confidence), int(max_iters), int(min_points),
+                                       _p(rvec), _p(tvec), _p(mask), _p(idx), _p(ninl), _p(iters), _p(status),
+                                       _p(ws), ws.numel(), _stream()), "fs_solve_pnp_ransac")
+    return {"rvec": rvec, "tvec": tvec, "mask": mask, "inlier_idx": idx, "n_inliers": ninl, "iters": iters,
+            "status": status}
+
+
+# ------------------------------------------------------------------------------------------- A8
+def rodrigues_batch(rvec: torch.Tensor) -> torch.Tensor:
+    lib = _lib.load()
+    rvec = _chk(rvec, torch.float64, "rvec").reshape(-1, 3)
+    R = torch.empty((rvec.shape[0], 3, 3), dtype=torch.float64, device=rvec.device)
+    _lib.check(lib.fs_rodrigues(_p(rvec), int(rvec.shape[0]), _p(R), _stream()), "fs_rodrigues")
+    return R
+
+
+def compose_trajectory(R: torch.Tensor, t: torch.Tensor, status: Optional[torch.Tensor] = None,
+                       T_init: Optional[np.ndarray] = None) -> torch.Tensor:
+    """T_cum[k] = T_init @ T_0 @ … @ T_k with T_k = [R_k | t_k] (mono_slam.py:115-118, stereo_slam.py:301-306)."""
+    lib = _lib.load()
+    R = _chk(R, torch.float64, "R")
+    t = _chk(t, torch.float64, "t")
+    n = int(R.shape[0])
+    out = torch.empty((max(n, 1), 4, 4), dtype=torch.float64, device=R.device)
+    T0 = None
+    if T_init is not None:
+        T0 = np.ascontiguousarray(T_init, dtype=np.float64)
+        T0p = T0.ctypes.data_as(C.c_void_p)
+    else:
+        T0p = None
+    st = None if status is None else _chk(status, torch.int32, "status")
+    _lib.check(lib.fs_compose_trajectory(_p(R), _p(t), _p(st), n, T0p, _p(out), _stream()),
+               "fs_compose_trajectory")
+    return out[:n]
+
+
+def transform_points_batch(points3d: torch.Tensor, n_pts: torch.Tensor, T: torch.Tensor) -> torch.Tensor:
+    """T_cum @ [P; 1] for every pair (stereo_slam.py:309-311)."""
+    lib = _lib.load()
+    points3d = _chk(points3d, torch.float32, "points3d")
+    n_pts = _chk(n_pts, torch.int32, "n_pts")
+    T = _chk(T, torch.float64, "T")
+    P, n_max = int(points3d.shape[0]), int(points3d.shape[1])
+    out = torch.zeros_like(points3d)
+    _lib.check(lib.fs_transform_points(_p(points3d), _p(n_pts), P, n_max, _p(T), _p(out), _stream()),
+               "fs_transform_points")
+    return out
+
+
+# =========================================================================================== cv2-shaped
+class BFMatcher:
+    """Drop-in for ``cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)`` (stereo_slam.py:85) on uint8 [N, 32]
+    descriptors, and for ``NORM_L2`` on float32 [N, 256] unit descriptors."""
+
+    def __init__(self, normType: int = NORM_HAMMING, crossCheck: bool = False):
+        if normType not in (NORM_HAMMING, NORM_L2):
+            raise ValueError("only NORM_HAMMING and NORM_L2 are on the hot path")
+        self.normType = normType
+        self.crossCheck = bool(crossCheck)
+
+    def _run(self, d0, d1, ratio=None):
+        dev = _dev()
+        d0 = np.asarray(d0)
+        d1 = np.asarray(d1)
+        n0, n1 = d0.shape[0], d1.shape[0]
+        if n0 == 0 or n1 == 0:
+            return None, n0
+        if self.normType == NORM_HAMMING:
+            n_max = max(n0, n1)
+            bank = torch.zeros((2, n_max, 32), dtype=torch.uint8, device=dev)
+            bank[0, :n0] = _to_cuda(d0, torch.uint8, dev)
+            bank[1, :n1] = _to_cuda(d1, torch.uint8, dev)
+            counts = torch.tensor([n0, n1], dtype=torch.int32, device=dev)
+            r = hamming_match_batch(bank, counts, [0], [1], cross_check=self.crossCheck, ratio=ratio)
+            return (r["matches0"][0, :n0].cpu().numpy(), r["dist0"][0, :n0].cpu().numpy().astype(np.float32),
+                    r["second0"][0, :n0].cpu().numpy().astype(np.float32)), n0
+        n_max = (max(n0, n1) + 127) // 128 * 128
+        bank = torch.zeros((2, 256, n_max), dtype=torch.float32, device=dev)
+        bank[0, :, :n0] = _to_cuda(d0, torch.float32, dev).T
+        bank[1, :, :n1] = _to_cuda(d1, torch.float32, dev).T
+        counts = torch.tensor([n0, n1], dtype=torch.int32, device=dev)
+        r = float_match_batch(bank, counts, [0], [1], ratio=ratio)
+        m0 = r["matches0"][0, :n0].cpu().numpy()
+        if not self.crossCheck:
+            raise NotImplementedError("NORM_L2 is exposed with crossCheck=True only (superglue.py:270 semantics)")
+        cos = r["score0"][0, :n0].cpu().numpy()
+        cos2 = r["second0"][0, :n0].cpu().numpy()
+        d = np.sqrt(np.maximum(0.0, 2.0 - 2.0 * cos)).astype(np.float32)
+        d2 = np.sqrt(np.maximum(0.0, 2.0 - 2.0 * cos2)).astype(np.float32)
+        return (m0, d, d2), n0
+
+    def match(self, queryDescriptors, trainDescriptors):
+        """→ tuple of DMatch sorted by queryIdx, like cv2 (stereo_slam.py:234)."""
+        res, n0 = self._run(queryDescriptors, trainDescriptors)
+        if res is None:
+            return ()
+        m0, d, _ = res
+        return tuple(DMatch(int(q), int(m0[q]), float(d[q])) for q in range(n0) if m0[q] >= 0)
+
+    def ratioMatch(self, queryDescriptors, trainDescriptors, ratio: float = 0.7):
+        """knnMatch(k=2) + Lowe ratio in one call (ORB_SLAM3/src/Frame.cc:1144-1151 semantics)."""
+        res, n0 = self._run(queryDescriptors, trainDescriptors, ratio=ratio)
+        if res is None:
+            return ()
+        m0, d, _ = res
+        return tuple(DMatch(int(q), int(m0[q]), float(d[q])) for q in range(n0) if m0[q] >= 0)
+
+
+def match_mutual_nn(descriptors0, descriptors1, *, scale: float = 1.0, threshold: Optional[float] = None,
+                    ratio: Optional[float] = None, exact_fp32: bool = False):
+    """Tail of SuperGlue.forward on the raw contraction (superglue.py:259-260, :268-278).
+
+    descriptors0 [256, N0], descriptors1 [256, N1] float32 (SuperPoint layout) →
+    dict(matches0, matches1, matching_scores0, matching_scores1) with -1 for unmatched, like the reference."""
+    dev = _dev()
+    d0 = np.asarray(descriptors0, dtype=np.float32)
+    d1 = np.asarray(descriptors1, dtype=np.float32)
+    n0, n1 = d0.shape[1], d1.shape[1]
+    if n0 == 0 or n1 == 0:  # superglue.py:235-242
+        return {"matches0": np.full((n0,), -1, np.int64), "matches1": np.full((n1,), -1, np.int64),
+                "matching_scores0": np.zeros((n0,), np.float32), "matching_scores1": np.zeros((n1,), np.float32)}
+    n_max = (max(n0, n1) + 127) // 128 * 128
+    bank = torch.zeros((2, 256, n_max), dtype=torch.float32, device=dev)
+    bank[0, :, :n0] = _to_cuda(d0, torch.float32, dev)
+    bank[1, :, :n1] = _to_cuda(d1, torch.float32, dev)
+    counts = torch.tensor([n0, n1], dtype=torch.int32, device=dev)
+    r = float_match_batch(bank, counts, [0], [1], scale=scale, threshold=threshold, ratio=ratio,
+                          exact_fp32=exact_fp32)
+    m0 = r["matches0"][0, :n0].cpu().numpy().astype(np.int64)
+    m1 = r["matches1"][0, :n1].cpu().numpy().astype(np.int64)
+    s0 = r["score0"][0, :n0].cpu().numpy()
+    ms0 = np.where(m0 >= 0, s0, 0.0).astype(np.float32)
+    ms1 = np.zeros((n1,), np.float32)
+    ms1[m0[m0 >= 0]] = ms0[m0 >= 0]
+    return {"matches0": m0, "matches1": m1, "matching_scores0": ms0, "matching_scores1": ms1}
+
+
+def _corr_batch(p0, p1, dev):
+    p0 = np.ascontiguousarray(np.asarray(p0, dtype=np.float32).reshape(-1, 2))
+    p1 = np.ascontiguousarray(np.asarray(p1, dtype=np.float32).reshape(-1, 2))
+    if p0.shape != p1.shape:
+        raise ValueError("point arrays must have the same shape")
+    n = p0.shape[0]
+    t0 = _to_cuda(p0, torch.float32, dev)[None]
+    t1 = _to_cuda(p1, torch.float32, dev)[None]
+    if n == 0:
+        t0 = torch.zeros((1, 1, 2), dtype=torch.float32, device=dev)
+        t1 = torch.zeros((1, 1, 2), dtype=torch.float32, device=dev)
+    return t0, t1, torch.tensor([n], dtype=torch.int32, device=dev), n
+
+
+def findEssentialMat(points1, points2, focal: float = 1.0, pp=(0.0, 0.0), method: int = RANSAC,
+                     prob: float = 0.999, threshold: float = 1.0, maxIters: int = 1000):
+    """cv2.findEssentialMat(p0, p1, focal=, pp=, method=cv2.RANSAC, prob=, threshold=) (mono_slam.py:111).
+    → (E [3,3] float64, mask [N,1] uint8 in {0,1}); (None, None) below 5 points, like cv2."""
+    if method != RANSAC:
+        raise ValueError("only method=cv2.RANSAC is on the hot path")
+    dev = _dev()
+    t0, t1, nc, n = _corr_batch(points1, points2, dev)
+    if n < 5:
+        return None, None
+    r = find_essential_batch(t0, t1, nc, focal=focal, pp=pp, prob=prob, threshold=threshold, max_iters=maxIters)
+    if int(r["status"][0].item()) != 0:
+        return None, None
+    return r["E"][0].cpu().numpy(), r["mask"][0, :n].cpu().numpy().reshape(-1, 1)
+
+
+def recoverPose(E, points1, points2, focal: float = 1.0, pp=(0.0, 0.0), distanceThresh: float = 50.0):
+    """cv2.recoverPose(E, p0, p1, focal=, pp=) (mono_slam.py:112) → (n_good, R, t [3,1], mask [N,1] in {0,255})."""
+    dev = _dev()
+    t0, t1, nc, n = _corr_batch(points1, points2, dev)
+    Et = _to_cuda(np.asarray(E, dtype=np.float64).reshape(1, 3, 3), torch.float64, dev)
+    r = recover_pose_batch(Et, t0, t1, nc, focal=focal, pp=pp, distance_thresh=distanceThresh)
+    return (int(r["n_good"][0].item()), r["R"][0].cpu().numpy(), r["t"][0].cpu().numpy().reshape(3, 1),
+            r["mask"][0, :n].cpu().numpy().reshape(-1, 1))
+
+
+def solvePnPRansac(objectPoints, imagePoints, cameraMatrix, distCoeffs, reprojectionError: float = 8.0,
+                   confidence: float = 0.99, iterationsCount: int = 100, flags: int = SOLVEPNP_ITERATIVE):
+    """cv2.solvePnPRansac(P3, p2, K, dist, reprojectionError=, confidence=, iterationsCount=, flags=ITERATIVE)
+    (stereo_slam.py:294-295) → (ok, rvec [3,1], tvec [3,1], inliers [I,1] int32)."""
+    if flags != SOLVEPNP_ITERATIVE:
+        raise ValueError("only SOLVEPNP_ITERATIVE is on the hot path")
+    dev = _dev()
+    P3 = np.ascontiguousarray(np.asarray(objectPoints, dtype=np.float32).reshape(-1, 3))
+    p2 = np.ascontiguousarray(np.asarray(imagePoints, dtype=np.float32).reshape(-1, 2))
+    n = P3.shape[0]
+    if n != p2.shape[0]:
+        raise ValueError("objectPoints / imagePoints length mismatch")
+    if n < 4:
+        raise ValueError("solvePnPRansac needs at least 4 points (cv2 asserts npoints >= 4)")
+    cam = camera_from_K(cameraMatrix, distCoeffs)
+    r = solve_pnp_ransac_batch(_to_cuda(P3, torch.float32, dev)[None], _to_cuda(p2, torch.float32, dev)[None],
+                               torch.tensor([n], dtype=torch.int32, device=dev), camera=cam,
+                               reproj_error=reprojectionError, confidence=confidence, max_iters=iterationsCount,
+                               min_points=5)
+    ok = int(r["status"][0].item()) == 0
+    ni = int(r["n_inliers"][0].item())
+    inl = r["inlier_idx"][0, :ni].cpu().numpy().astype(np.int32).reshape(-1, 1) if ok else None
+    return ok, r["rvec"][0].cpu().numpy().reshape(3, 1), r["tvec"][0].cpu().numpy().reshape(3, 1), inl
+
+
+def Rodrigues(rvec):
+    """cv2.Rodrigues(rvec) (stereo_slam.py:298) → (R [3,3], None)."""
+    dev = _dev()
+    r = _to_cuda(np.asarray(rvec, dtype=np.float64).reshape(1, 3), torch.float64, dev)
+    return rodrigues_batch(r)[0].cpu().numpy(), None

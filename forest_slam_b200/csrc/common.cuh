@@ -1,0 +1,60 @@
+// common.cuh — shared helpers for the forestslam_b200 C-ABI library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/forestslam_b200.h"
+
+namespace fs {
+
+// thread-local last-error text returned by fs_last_error_string()
+void set_error(const char* fmt, ...);
+
+inline int check_cuda(cudaError_t e, const char* what) {
+    if (e != cudaSuccess) {
+        set_error("%s: %s", what, cudaGetErrorString(e));
+        return FS_ERR_CUDA;
+    }
+    return FS_OK;
+}
+
+#define FS_CUDA(call)                                         \
+    do {                                                      \
+        int _s = fs::check_cuda((call), #call);               \
+        if (_s != FS_OK) return _s;                           \
+    } while (0)
+
+#define FS_LAUNCH_CHECK(name)                                 \
+    do {                                                      \
+        int _s = fs::check_cuda(cudaGetLastError(), name);    \
+        if (_s != FS_OK) return _s;                           \
+    } while (0)
+
+#define FS_REQUIRE(cond, msg)                                 \
+    do {                                                      \
+        if (!(cond)) {                                        \
+            fs::set_error("bad argument: %s", msg);           \
+            return FS_ERR_BAD_ARG;                            \
+        }                                                     \
+    } while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+int sm_count();
+
+// carve a workspace pointer
+struct Carver {
+    char* base;
+    size_t off;
+    explicit Carver(void* p) : base((char*)p), off(0) {}
+    template <class T>
+    T* take(size_t n) {
+        off = align_up(off, 256);
+        T* r = (T*)(base + off);
+        off += n * sizeof(T);
+        return r;
+    }
+};
+
+}  // namespace fs

@@ -1,0 +1,202 @@
+// cvmath.cuh — device restatements of the small OpenCV numerical building blocks the RANSAC / pose
+// kernels need: cv::RNG (multiply-with-carry), the one-sided Jacobi SVD of core/lapack.cpp including
+// its deterministic completion of missing singular vectors, cv::solvePoly's Durand-Kerner iteration,
+// RANSACUpdateNumIters, Rodrigues.  OpenCV is a third-party dependency of the reference that is not
+// vendored under /root/reference (Dockerfile:62-67); the algorithms are restated from their published
+// form and pinned stage by stage against the cv2 4.13 binary by oracle/opencv_replay.py + tests/.
+//
+// Files including this header are compiled with -fmad=false: OpenCV's x86-64 baseline build (SSE3)
+// cannot contract a*b+c, and the float32 inlier tests downstream are sensitive to the last bit.
+#pragma once
+#include <cuda_runtime.h>
+#include <float.h>
+#include <math.h>
+#include <stdint.h>
+
+#define CVM_HD __host__ __device__ inline
+
+namespace cvm {
+
+// ------------------------------------------------------------------------------------------ cv::RNG
+struct RNG {
+    unsigned long long state;
+    __host__ __device__ explicit RNG(unsigned long long s = 0xFFFFFFFFFFFFFFFFull) : state(s ? s : 0xFFFFFFFFull) {}
+    __host__ __device__ unsigned next() {
+        state = (unsigned long long)(unsigned)state * 4164903690ull + (unsigned)(state >> 32);
+        return (unsigned)state;
+    }
+    __host__ __device__ int uniform(int a, int b) { return a == b ? a : a + (int)(next() % (unsigned)(b - a)); }
+};
+
+// RANSACUpdateNumIters (calib3d/ptsetreg.cpp)
+CVM_HD int ransac_update_num_iters(double p, double ep, int model_points, int max_iters) {
+    p = fmax(p, 0.);
+    p = fmin(p, 1.);
+    ep = fmax(ep, 0.);
+    ep = fmin(ep, 1.);
+    double num = fmax(1. - p, DBL_MIN);
+    double denom = 1. - pow(1. - ep, (double)model_points);
+    if (denom < DBL_MIN) return 0;
+    num = log(num);
+    denom = log(denom);
+    return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
+}
+
+// ------------------------------------------------------------------------------------------ JacobiSVD
+// JacobiSVDImpl_<double> (core/lapack.cpp).  At holds N row vectors of length M (the matrix whose rows
+// are orthogonalised in place), Vt the N x N accumulated rotations, W the singular values.  After the
+// sweeps the rows are sorted by decreasing norm and rows 0..N1-1 of At are normalised; rows whose norm
+// is <= DBL_MIN (and rows N..N1-1, the missing vectors of a FULL_UV request) are filled with the
+// deterministic pseudo-random completion.  LDA is the row stride of At (>= M), At must have N1 rows.
+template <int M, int N, int N1>
+CVM_HD void jacobi_svd(double* At, int lda, double* W, double* Vt /* N*N or nullptr */) {
+    const double eps = DBL_EPSILON * 10, minval = DBL_MIN;
+    const int max_iter = M > 30 ? M : 30;
+    for (int i = 0; i < N; i++) {
+        double sd = 0;
+        for (int k = 0; k < M; k++) {
+            double t = At[i * lda + k];
+            sd += t * t;
+        }
+        W[i] = sd;
+        if (Vt) {
+            for (int k = 0; k < N; k++) Vt[i * N + k] = 0;
+            Vt[i * N + i] = 1;
+        }
+    }
+    for (int iter = 0; iter < max_iter; iter++) {
+        bool changed = false;
+        for (int i = 0; i < N - 1; i++)
+            for (int j = i + 1; j < N; j++) {
+                double* Ai = At + i * lda;
+                double* Aj = At + j * lda;
+                double a = W[i], p = 0, b = W[j];
+                for (int k = 0; k < M; k++) p += Ai[k] * Aj[k];
+                if (fabs(p) <= eps * sqrt(a * b)) continue;
+                p *= 2;
+                double beta = a - b, gamma = hypot(p, beta), c, s;
+                if (beta < 0) {
+                    double delta = (gamma - beta) * 0.5;
+                    s = sqrt(delta / gamma);
+                    c = p / (gamma * s * 2);
+                } else {
+                    c = sqrt((gamma + beta) / (gamma * 2));
+                    s = p / (gamma * c * 2);
+                }
+                a = b = 0;
+                for (int k = 0; k < M; k++) {
+                    double t0 = c * Ai[k] + s * Aj[k];
+                    double t1 = -s * Ai[k] + c * Aj[k];
+                    Ai[k] = t0;
+                    Aj[k] = t1;
+                    a += t0 * t0;
+                    b += t1 * t1;
+                }
+                W[i] = a;
+                W[j] = b;
+                changed = true;
+                if (Vt) {
+                    double* Vi = Vt + i * N;
+                    double* Vj = Vt + j * N;
+                    for (int k = 0; k < N; k++) {
+                        double t0 = c * Vi[k] + s * Vj[k];
+                        double t1 = -s * Vi[k] + c * Vj[k];
+                        Vi[k] = t0;
+                        Vj[k] = t1;
+                    }
+                }
+            }
+        if (!changed) break;
+    }
+    for (int i = 0; i < N; i++) {
+        double sd = 0;
+        for (int k = 0; k < M; k++) {
+            double t = At[i * lda + k];
+            sd += t * t;
+        }
+        W[i] = sqrt(sd);
+    }
+    for (int i = 0; i < N - 1; i++) {
+        int j = i;
+        for (int k = i + 1; k < N; k++)
+            if (W[j] < W[k]) j = k;
+        if (i != j) {
+            double t = W[i];
+            W[i] = W[j];
+            W[j] = t;
+            if (Vt) {
+                for (int k = 0; k < M; k++) {
+                    t = At[i * lda + k];
+                    At[i * lda + k] = At[j * lda + k];
+                    At[j * lda + k] = t;
+                }
+                for (int k = 0; k < N; k++) {
+                    t = Vt[i * N + k];
+                    Vt[i * N + k] = Vt[j * N + k];
+                    Vt[j * N + k] = t;
+                }
+            }
+        }
+    }
+    if (!Vt) return;
+    RNG rng(0x12345678ull);
+    for (int i = 0; i < N1; i++) {
+        double sd = i < N ? W[i] : 0;
+        for (int ii = 0; ii < 100 && sd <= minval; ii++) {
+            const double val0 = 1. / M;
+            for (int k = 0; k < M; k++) At[i * lda + k] = (rng.next() & 256) != 0 ? val0 : -val0;
+            for (int iter = 0; iter < 2; iter++)
+                for (int j = 0; j < i; j++) {
+                    sd = 0;
+                    for (int k = 0; k < M; k++) sd += At[i * lda + k] * At[j * lda + k];
+                    double asum = 0;
+                    for (int k = 0; k < M; k++) {
+                        double t = At[i * lda + k] - sd * At[j * lda + k];
+                        At[i * lda + k] = t;
+                        asum += fabs(t);
+                    }
+                    asum = asum > eps * 100 ? 1 / asum : 0;
+                    for (int k = 0; k < M; k++) At[i * lda + k] *= asum;
+                }
+            sd = 0;
+            for (int k = 0; k < M; k++) {
+                double t = At[i * lda + k];
+                sd += t * t;
+            }
+            sd = sqrt(sd);
+        }
+        const double s = sd > minval ? 1 / sd : 0.;
+        for (int k = 0; k < M; k++) At[i * lda + k] *= s;
+    }
+}
+
+// cv::SVD::compute(A[R x C]) for R >= C (no transposition inside OpenCV): w[C], u[R x C] (columns = left
+// singular vectors), vt[C x C].  OpenCV feeds JacobiSVD with the transpose (rows = columns of A).
+template <int R, int C>
+CVM_HD void svd_tall(const double* A, double* w, double* u /* R*C or null */, double* vt) {
+    double At[C * R];
+    for (int i = 0; i < R; i++)
+        for (int j = 0; j < C; j++) At[j * R + i] = A[i * C + j];
+    jacobi_svd<R, C, C>(At, R, w, vt);
+    if (u)
+        for (int i = 0; i < R; i++)
+            for (int j = 0; j < C; j++) u[i * C + j] = At[j * R + i];
+}
+
+// ------------------------------------------------------------------------------------------ Rodrigues
+CVM_HD void rodrigues_vec2mat(const double* r, double* R) {
+    const double rx = r[0], ry = r[1], rz = r[2];
+    const double theta = sqrt(rx * rx + ry * ry + rz * rz);
+    if (theta < DBL_EPSILON) {
+        R[0] = 1; R[1] = 0; R[2] = 0; R[3] = 0; R[4] = 1; R[5] = 0; R[6] = 0; R[7] = 0; R[8] = 1;
+        return;
+    }
+    const double c = cos(theta), s = sin(theta), c1 = 1. - c, it = theta ? 1. / theta : 0.;
+    const double x = rx * it, y = ry * it, z = rz * it;
+    // R = c*I + c1*(r r^T) + s*[r]_x, element by element in that order (cvRodrigues2)
+    R[0] = (c + c1 * (x * x));            R[1] = (c1 * (x * y)) + s * (-z);    R[2] = (c1 * (x * z)) + s * y;
+    R[3] = (c1 * (x * y)) + s * z;        R[4] = (c + c1 * (y * y));           R[5] = (c1 * (y * z)) + s * (-x);
+    R[6] = (c1 * (x * z)) + s * (-y);     R[7] = (c1 * (y * z)) + s * x;       R[8] = (c + c1 * (z * z));
+}
+
+}  // namespace cvm

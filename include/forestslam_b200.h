@@ -1,0 +1,258 @@
+/*
+ * forestslam_b200.h — C ABI of the B200-native (sm_100a) matching + pose hot path of Forest-SLAM.
+ *
+ * This is the drop-in boundary.  The reference (si220/Forest-SLAM) has no FFI of its
+ * own: its boundary is a handful of cv2 / torch call expressions inside the frame loop of
+ * ros_ws/src/mono_slam.py and ros_ws/src/stereo_slam.py.  Every entry point below names the call
+ * expression it replaces.  The Python host mirror (forest_slam_b200/api.py) binds these with ctypes and
+ * re-exposes them under the cv2 names the scripts use; INTEGRATION.md shows the stub.
+ *
+ * Conventions (all entry points):
+ *   - every pointer is a DEVICE pointer unless the parameter name ends in `_host`;
+ *   - the caller owns every buffer (inputs, outputs, workspace); the library never allocates device
+ *     memory, never synchronises the device and enqueues only on `stream` (a cudaStream_t);
+ *   - a "frame bank" is a dense array [n_frames, n_max, ...] with a per-frame count array
+ *     `counts[n_frames]` (int32); a "pair list" is two int32 arrays pair_a / pair_b of frame indices.
+ *     Temporal sequences use (i, i+1); loop closure uses every (a, b), a < b;
+ *   - a "correspondence batch" is [n_pairs, n_max, ...] with per-pair counts `n_corr[n_pairs]`;
+ *   - return value: FS_OK (0) or a negative FSStatus.  Nothing throws across the ABI.
+ *     Per-pair degenerate inputs (fewer than 5 correspondences for E, fewer than 6 for the PnP gate of
+ *     stereo_slam.py:292) do not fail the call: they are reported in the per-pair `status` output.
+ *   - results are deterministic: same inputs, same bits, independent of batch split / GPU count.
+ */
+#ifndef FORESTSLAM_B200_H
+#define FORESTSLAM_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* fs_stream_t; /* cudaStream_t */
+
+typedef enum FSStatus {
+    FS_OK = 0,
+    FS_ERR_BAD_ARG = -1,         /* null pointer, negative size, n_max above the compiled limit */
+    FS_ERR_WORKSPACE = -2,       /* workspace_bytes smaller than fs_*_workspace_bytes() */
+    FS_ERR_CUDA = -3,            /* a CUDA runtime call failed; see fs_last_error_string() */
+    FS_ERR_UNSUPPORTED = -4      /* feature not available on this device (not sm_100) */
+} FSStatus;
+
+/* per-pair status codes written to `status[n_pairs]` by the RANSAC entry points */
+enum {
+    FS_PAIR_OK = 0,
+    FS_PAIR_TOO_FEW = 1,   /* <5 (E) or <6 (PnP gate, stereo_slam.py:292): outputs zeroed, mask all 0 */
+    FS_PAIR_NO_MODEL = 2   /* RANSAC found no model with >= 5 inliers (cv2 returns None / False) */
+};
+
+int fs_version(void);
+const char* fs_last_error_string(void);
+const char* fs_status_string(int status);
+/* number of SMs of the current device (grid sizing is done inside the library; exported for benches) */
+int fs_device_sm_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * A2  binary descriptor matching — replaces
+ *       bf = cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True)      stereo_slam.py:85
+ *       matches = bf.match(descs0, descs1)                        stereo_slam.py:234, :242
+ *     and the k=2 + Lowe-ratio variant (ORB_SLAM3/src/Frame.cc:1144-1151).
+ *     Distance definition: 256-bit Hamming (ORB_SLAM3/src/ORBmatcher.cc:2058-2074).
+ *
+ * desc      [n_frames, n_max, 32] u8      ORB-style descriptors, row-major, 16-byte aligned rows
+ * counts    [n_frames] i32                valid rows per frame (<= n_max)
+ * pair_a/b  [n_pairs] i32                 query frame / train frame of each pair
+ * cross_check  !=0: keep (q,t) only if t's best query is q (lowest index wins ties, both directions)
+ * ratio     <=0: off; else keep only if (double)best < (double)second * (double)ratio
+ *           (a query with a single train row has no second neighbour and is dropped, like knnMatch k=2)
+ * outputs, each [n_pairs, n_max] i32:
+ *   matches0   train index of query q, or -1       (what DMatch.queryIdx/trainIdx encode, sorted by q)
+ *   dist0      best Hamming distance of q (valid even when matches0 is -1); second0 the runner-up
+ *              (INT32_MAX when there is none); either may be NULL
+ *   matches1   query index matched to train t, or -1; may be NULL
+ * n_matches [n_pairs] i32  number of q with matches0 >= 0; may be NULL
+ * ---------------------------------------------------------------------------------------------- */
+size_t fs_hamming_match_workspace_bytes(int n_pairs, int n_max);
+int fs_hamming_match(const uint8_t* desc, int n_frames, int n_max, const int32_t* counts,
+                     const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                     int cross_check, float ratio,
+                     int32_t* matches0, int32_t* dist0, int32_t* second0, int32_t* matches1,
+                     int32_t* n_matches,
+                     void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A1  float descriptor matching — replaces the tail of SuperGlue.forward that mono_slam.py:100-103 and
+ *     stereo_slam.py:210-213, :221-224 consume:
+ *       scores = einsum('bdn,bdm->bnm', d0, d1)                   superglue.py:259   (dense contraction)
+ *       max0, max1 = scores.max(2), scores.max(1) ; mutual check ; threshold ; -1 fill   superglue.py:268-278
+ *     plus the Lowe ratio of the north star on L2 distance d = sqrt(max(0, 2 - 2 s)) of unit vectors.
+ *
+ * Two-step: fs_float_prepare() turns a frame bank of channel-major fp32 descriptors (SuperPoint layout
+ * [256, n], superpoint.py:90-91) into the K-major split-bf16 operand bank the tensor-core kernel reads
+ * (once per FRAME, not per pair); fs_float_match() then runs the tcgen05 contraction with the fused
+ * row top-2 epilogue for both directions and the mutual / threshold / ratio finalisation.
+ *
+ * desc_f32   [n_frames, 256, n_max] f32   channel-major
+ * operands   [n_frames, n_max, 512] bf16  (hi | lo split; rows >= count are zero)
+ * scale      multiplies the raw dot product (superglue.py:260 uses 1/sqrt(256) = 0.0625); 1.0 = cosine
+ * threshold  keep only if scaled best score > threshold (use -inf to disable)
+ * ratio      <=0: off; else keep only if d_best < ratio * d_second (float32, strict), d from raw cosine
+ * outputs [n_pairs, n_max]: matches0 i32, score0 f32 (scaled best), second0 f32 (scaled runner-up,
+ *   -inf when none), matches1 i32; n_matches [n_pairs].  score0/second0/matches1/n_matches may be NULL.
+ * ---------------------------------------------------------------------------------------------- */
+#define FS_FLOAT_DIM 256
+int fs_float_prepare(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
+                     void* operands_bf16, fs_stream_t stream);
+size_t fs_float_match_workspace_bytes(int n_pairs, int n_max);
+int fs_float_match(const void* operands_bf16, int n_frames, int n_max, const int32_t* counts,
+                   const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                   float scale, float threshold, float ratio,
+                   int32_t* matches0, float* score0, float* second0, int32_t* matches1,
+                   int32_t* n_matches,
+                   void* workspace, size_t workspace_bytes, fs_stream_t stream);
+/* exact-fp32 CUDA-core variant of the same operator working directly on desc_f32 (used for n_max that
+ * are not a multiple of 128 and as the in-library cross-check of the tensor-core path) */
+int fs_float_match_fp32(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
+                        const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                        float scale, float threshold, float ratio,
+                        int32_t* matches0, float* score0, float* second0, int32_t* matches1,
+                        int32_t* n_matches,
+                        void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A3  match gather / order-preserving compaction — replaces
+ *       valid = matches > -1 ; mkpts0 = kpts0[valid] ; mkpts1 = kpts1[matches[valid]]
+ *     mono_slam.py:106-108, stereo_slam.py:216-218, :227-229 (ascending query index: this order defines
+ *     the correspondence indices the RANSAC sampler draws).
+ *
+ * kpts     [n_frames, n_max, 2] f32 (x, y) pixels
+ * matches0 [n_pairs, n_max] i32
+ * mkpts0/1 [n_pairs, n_max, 2] f32 (first n_corr[p] rows valid), n_corr [n_pairs] i32
+ * src_idx  [n_pairs, n_max] i32 query index of every compacted row; may be NULL
+ * ---------------------------------------------------------------------------------------------- */
+int fs_gather_matches(const float* kpts, int n_frames, int n_max, const int32_t* counts,
+                      const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                      const int32_t* matches0,
+                      float* mkpts0, float* mkpts1, int32_t* n_corr, int32_t* src_idx,
+                      fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A6  stereo "triangulation": disparity -> depth -> pin-hole back-projection -> depth gate — replaces
+ *       depth = fx * baseline / disparity_map (0 and -1 -> 0.1)     stereo_slam.py:117-121, :264-271
+ *       Z = depth[int(y), int(x)] ; X = (x-cx)/fx*Z ; Y = (y-cy)/fy*Z  stereo_slam.py:274-284
+ *       valid = (Z > 0.1) & (Z < 1000) ; filter points3D and mkpts1    stereo_slam.py:287-289
+ *
+ * pts        [n_points, 2] f32
+ * disparity  either per point [n_points] f32 (map_h == 0) or dense maps [n_maps, map_h, map_w] f32
+ *            looked up at (int(y), int(x)) of map `map_index[i]` (NULL: map 0); disparities are the
+ *            raw SGBM/16 values: exactly 0 and exactly -1 are replaced by 0.1 as the reference does
+ * points3d   [n_points, 3] f32,  valid [n_points] u8 (1 inside the gate)
+ * Arithmetic is float32 in the reference's operation order (NumPy-1.x value-based casting keeps the
+ * f32 keypoints f32); SURVEY.md §8a row A6.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct FSCamera {
+    double fx, fy, cx, cy;
+    double dist[5]; /* k1 k2 p1 p2 k3 (stereo_slam.py:50) */
+} FSCamera;
+
+int fs_backproject_stereo(const float* pts, const float* disparity, const int32_t* map_index,
+                          int64_t n_points, int map_h, int map_w,
+                          const FSCamera* cam_host, double baseline, double z_min, double z_max,
+                          float* points3d, uint8_t* valid, fs_stream_t stream);
+/* batched + fused filter (stereo_slam.py:288-289): keeps rows with valid depth, in order, for both the
+ * 3-D points and the partner 2-D points; out arrays [n_pairs, n_max, 3|2], n_out [n_pairs]. */
+int fs_backproject_filter(const float* mkpts0, const float* mkpts1, const float* disparity,
+                          const int32_t* n_corr, int n_pairs, int n_max,
+                          const FSCamera* cam_host, double baseline, double z_min, double z_max,
+                          float* points3d_out, float* pts2d_out, int32_t* n_out, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A4  essential-matrix RANSAC — replaces
+ *       E, mask = cv2.findEssentialMat(mkpts0, mkpts1, focal=K0[0,0], pp=(K0[0,2],K0[1,2]),
+ *                                      method=cv2.RANSAC, prob=0.999, threshold=1.0)   mono_slam.py:111
+ *     OpenCV semantics reproduced: points normalised by one focal and pp; thr /= focal; sampler =
+ *     cv::RNG(2^64-1) MWC, 5 distinct indices per iteration; Nister 5-point (<=10 candidates, solver
+ *     order); Sampson error cast to float32, inlier iff <= (float)thr^2; best updated on strictly
+ *     greater count (and > 4); iteration cap shrinks adaptively; no refit.
+ *
+ * mkpts0/1 [n_pairs, n_max, 2] f32, n_corr [n_pairs]
+ * E        [n_pairs, 9] f64 row-major, mask [n_pairs, n_max] u8 in {0,1},
+ * n_inliers [n_pairs] i32, iters_run [n_pairs] i32 (may be NULL), status [n_pairs] i32
+ * ---------------------------------------------------------------------------------------------- */
+size_t fs_find_essential_workspace_bytes(int n_pairs, int n_max, int max_iters);
+int fs_find_essential_ransac(const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                             int n_pairs, int n_max,
+                             double focal, double pp_x, double pp_y,
+                             double prob, double threshold, int max_iters,
+                             double* E, uint8_t* mask, int32_t* n_inliers, int32_t* iters_run,
+                             int32_t* status,
+                             void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
+/* the sampler alone (OpenCV RANSACPointSetRegistrator::getSubset replay): subsets [n_pairs, max_iters, 5] */
+int fs_ransac_subsets(const int32_t* n_corr, int n_pairs, int max_iters, int32_t* subsets,
+                      fs_stream_t stream);
+
+/* hypothesis scoring sweeps (BASELINE config 4: 1k..64k hypotheses per frame pair, one warp per
+ * hypothesis, correspondences staged in shared memory):
+ *   models_E [n_pairs, n_hyp, 9] f64 -> counts [n_pairs, n_hyp] i32 (Sampson, normalised points)
+ *   models_rt [n_pairs, n_hyp, 6] f64 (rvec | tvec) -> counts (reprojection with k1,k2,p1,p2,k3)   */
+int fs_score_essential(const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                       int n_pairs, int n_max, double focal, double pp_x, double pp_y, double threshold,
+                       const double* models_E, int n_hyp, int32_t* counts, fs_stream_t stream);
+int fs_score_pnp(const float* points3d, const float* pts2d, const int32_t* n_corr,
+                 int n_pairs, int n_max, const FSCamera* cam_host, double reproj_error,
+                 const double* models_rt, int n_hyp, int32_t* counts, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A5  pose from E — replaces
+ *       _, R, t, _ = cv2.recoverPose(E, mkpts0, mkpts1, focal=..., pp=...)           mono_slam.py:112
+ *     decomposeEssentialMat -> 4 (R,t) combos -> DLT triangulation of ALL points (no mask is passed by
+ *     the reference) -> cheirality / distance (50) gates -> arg-max (first wins).
+ * R [n_pairs, 9] f64, t [n_pairs, 3] f64 (unit norm), mask [n_pairs, n_max] u8 in {0,255},
+ * n_good [n_pairs] i32.  Pairs whose status_in (may be NULL) is not FS_PAIR_OK are skipped (R = I, t = 0).
+ * ---------------------------------------------------------------------------------------------- */
+int fs_recover_pose(const double* E, const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                    const int32_t* status_in, int n_pairs, int n_max,
+                    double focal, double pp_x, double pp_y, double distance_thresh,
+                    double* R, double* t, uint8_t* mask, int32_t* n_good, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A7  PnP RANSAC — replaces
+ *       _, rvec, tvec, inliers = cv2.solvePnPRansac(points3D, mkpts1_l, K0, dist_coeffs_l,
+ *             reprojectionError=1.0, confidence=0.99, iterationsCount=1000,
+ *             flags=cv2.SOLVEPNP_ITERATIVE)                                      stereo_slam.py:294-295
+ *     OpenCV semantics: inputs as float32; same sampler as A4; EPnP on each 5-subset (points
+ *     undistorted first); projectPoints with distortion -> float32 -> squared error <= thr^2 in
+ *     float32; adaptive stop; final Levenberg-Marquardt refit (SOLVEPNP_ITERATIVE) on the inlier set.
+ * points3d [n_pairs, n_max, 3] f32, pts2d [n_pairs, n_max, 2] f32, n_corr [n_pairs]
+ * rvec, tvec [n_pairs, 3] f64; mask [n_pairs, n_max] u8 {0,1}; inlier_idx [n_pairs, n_max] i32
+ * ascending (first n_inliers valid; may be NULL); status as above (FS_PAIR_TOO_FEW when n < min_points,
+ * the reference's gate is 6).
+ * ---------------------------------------------------------------------------------------------- */
+size_t fs_solve_pnp_workspace_bytes(int n_pairs, int n_max, int max_iters);
+int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, const int32_t* n_corr,
+                        int n_pairs, int n_max, const FSCamera* cam_host,
+                        double reproj_error, double confidence, int max_iters, int min_points,
+                        double* rvec, double* tvec, uint8_t* mask, int32_t* inlier_idx,
+                        int32_t* n_inliers, int32_t* iters_run, int32_t* status,
+                        void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * A8  pose algebra — replaces cv2.Rodrigues + [R|t] + T_cum = T_cum @ T (stereo_slam.py:298-306,
+ *     mono_slam.py:115-118) and the map-point transform T_cum @ [P;1] (stereo_slam.py:309-311).
+ * fs_rodrigues:   rvec [n,3] f64 -> R [n,9] f64
+ * fs_compose_trajectory: relative (R [n,9], t [n,3]) -> cumulative T [n,16] f64, T_k = T_0 ... T_k
+ *     (sequential by definition; one warp walks the chain), skipping entries with status != 0
+ * fs_transform_points: points [n_pairs, n_max, 3] f32 by T [n_pairs, 16] f64 -> out f32
+ * ---------------------------------------------------------------------------------------------- */
+int fs_rodrigues(const double* rvec, int n, double* R, fs_stream_t stream);
+int fs_compose_trajectory(const double* R, const double* t, const int32_t* status, int n,
+                          const double* T_init_host, double* T_cum, fs_stream_t stream);
+int fs_transform_points(const float* points3d, const int32_t* n_pts, int n_pairs, int n_max,
+                        const double* T, float* out, fs_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FORESTSLAM_B200_H */
