@@ -253,4 +253,17 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
     return count;
 }
 
+// EMEstimatorCallback::computeError for one correspondence (double arithmetic in OpenCV's operation order,
+// float32 result) — the residual behind the inlier mask of cv2.findEssentialMat (mono_slam.py:111)
+CVM_HD float sampson_f32(const double* E, double x1, double y1, double x2, double y2) {
+    const double Ex1_0 = (E[0] * x1 + E[1] * y1) + E[2];
+    const double Ex1_1 = (E[3] * x1 + E[4] * y1) + E[5];
+    const double Ex1_2 = (E[6] * x1 + E[7] * y1) + E[8];
+    const double Etx2_0 = (E[0] * x2 + E[3] * y2) + E[6];
+    const double Etx2_1 = (E[1] * x2 + E[4] * y2) + E[7];
+    const double x2tEx1 = (x2 * Ex1_0 + y2 * Ex1_1) + Ex1_2;
+    const double a = Ex1_0 * Ex1_0, b = Ex1_1 * Ex1_1, c = Etx2_0 * Etx2_0, d = Etx2_1 * Etx2_1;
+    return (float)(x2tEx1 * x2tEx1 / (((a + b) + c) + d));
+}
+
 }  // namespace cvm

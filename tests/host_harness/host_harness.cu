@@ -2,6 +2,8 @@
 // (csrc/cvmath.cuh, fivepoint.cuh, ...) for the HOST so that the CPU test-suite can pin the exact code the
 // kernels execute against cv2 without a GPU.  Never loaded by the product path.
 #include "../../forest_slam_b200/csrc/fivepoint.cuh"
+#include "../../forest_slam_b200/csrc/posemath.cuh"
+#include <vector>
 
 extern "C" {
 
@@ -32,4 +34,90 @@ int hh_update_num_iters(double p, double ep, int model_points, int max_iters) {
 
 void hh_svd33(const double* A, double* w, double* u, double* vt) { cvm::svd_tall<3, 3>(A, w, u, vt); }
 void hh_svd44(const double* A, double* w, double* u, double* vt) { cvm::svd_tall<4, 4>(A, w, u, vt); }
+
+// serial findEssentialMat(RANSAC) built from the SAME header code the kernel k_essential_ransac runs
+// (sampler, five_point, sampson_f32, adaptive cap): returns the number of inliers, fills E[9], mask[n], iters.
+int hh_find_essential(const float* p0, const float* p1, int n, double focal, double ppx, double ppy, double prob,
+                      double threshold, int max_iters, double* E_out, unsigned char* mask, int* iters) {
+    if (n < 5) return -1;
+    std::vector<double> x1(n), y1(n), x2(n), y2(n);
+    for (int i = 0; i < n; i++) {
+        x1[i] = ((double)p0[2 * i] - ppx) / focal;
+        y1[i] = ((double)p0[2 * i + 1] - ppy) / focal;
+        x2[i] = ((double)p1[2 * i] - ppx) / focal;
+        y2[i] = ((double)p1[2 * i + 1] - ppy) / focal;
+    }
+    double thr = threshold / ((focal + focal) / 2);
+    const float thr2 = (float)(thr * thr);
+    cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
+    int niters = max_iters > 1 ? max_iters : 1, best = 0, it = 0;
+    double bestE[9] = {0};
+    for (it = 0; it < niters; it++) {
+        int idx[5];
+        if (n == 5) {
+            for (int i = 0; i < 5; i++) idx[i] = i;
+        } else {
+            for (int i = 0; i < 5; i++) {
+                int v;
+                bool dup;
+                do {
+                    v = rng.uniform(0, n);
+                    dup = false;
+                    for (int k = 0; k < i; k++) dup |= idx[k] == v;
+                } while (dup);
+                idx[i] = v;
+            }
+        }
+        double q1[5][2], q2[5][2], models[90];
+        for (int i = 0; i < 5; i++) {
+            q1[i][0] = x1[idx[i]]; q1[i][1] = y1[idx[i]];
+            q2[i][0] = x2[idx[i]]; q2[i][1] = y2[idx[i]];
+        }
+        const int nm = cvm::five_point(q1, q2, models);
+        for (int k = 0; k < nm; k++) {
+            int c = 0;
+            for (int i = 0; i < n; i++) c += cvm::sampson_f32(models + 9 * k, x1[i], y1[i], x2[i], y2[i]) <= thr2;
+            if (c > (best > 4 ? best : 4)) {
+                best = c;
+                for (int i = 0; i < 9; i++) bestE[i] = models[9 * k + i];
+                niters = cvm::ransac_update_num_iters(prob, (double)(n - c) / n, 5, niters);
+            }
+        }
+        if (n == 5) { it = 1; break; }
+    }
+    *iters = it;
+    for (int i = 0; i < 9; i++) E_out[i] = bestE[i];
+    for (int i = 0; i < n; i++)
+        mask[i] = best ? (n == 5 ? 1 : (cvm::sampson_f32(bestE, x1[i], y1[i], x2[i], y2[i]) <= thr2)) : 0;
+    return n == 5 && best ? 5 : best;
+}
+
+// recoverPose from the same header code as k_recover_pose
+int hh_recover_pose(const double* E, const float* p0, const float* p1, int n, double focal, double ppx, double ppy,
+                    double dist, double* R_out, double* t_out, unsigned char* mask) {
+    double R1[9], R2[9], tp[3], tm[3];
+    cvm::decompose_essential(E, R1, R2, tp);
+    for (int i = 0; i < 3; i++) tm[i] = -tp[i];
+    int cnt[4] = {0, 0, 0, 0};
+    std::vector<unsigned char> bits(n);
+    for (int i = 0; i < n; i++) {
+        const double x1 = ((double)p0[2 * i] - ppx) / focal, y1 = ((double)p0[2 * i + 1] - ppy) / focal;
+        const double x2 = ((double)p1[2 * i] - ppx) / focal, y2 = ((double)p1[2 * i + 1] - ppy) / focal;
+        const bool m0 = cvm::cheirality(R1, tp, x1, y1, x2, y2, dist);
+        const bool m1 = cvm::cheirality(R2, tp, x1, y1, x2, y2, dist);
+        const bool m2 = cvm::cheirality(R1, tm, x1, y1, x2, y2, dist);
+        const bool m3 = cvm::cheirality(R2, tm, x1, y1, x2, y2, dist);
+        cnt[0] += m0; cnt[1] += m1; cnt[2] += m2; cnt[3] += m3;
+        bits[i] = (unsigned char)(m0 | (m1 << 1) | (m2 << 2) | (m3 << 3));
+    }
+    int best;
+    if (cnt[0] >= cnt[1] && cnt[0] >= cnt[2] && cnt[0] >= cnt[3]) best = 0;
+    else if (cnt[1] >= cnt[0] && cnt[1] >= cnt[2] && cnt[1] >= cnt[3]) best = 1;
+    else if (cnt[2] >= cnt[0] && cnt[2] >= cnt[1] && cnt[2] >= cnt[3]) best = 2;
+    else best = 3;
+    for (int i = 0; i < 9; i++) R_out[i] = (best & 1) ? R2[i] : R1[i];
+    for (int i = 0; i < 3; i++) t_out[i] = (best & 2) ? tm[i] : tp[i];
+    for (int i = 0; i < n; i++) mask[i] = ((bits[i] >> best) & 1) ? 255 : 0;
+    return cnt[best];
+}
 }

@@ -1,0 +1,177 @@
+"""CPU suite: pins the oracle (oracle/cv_literal.py, oracle/opencv_replay.py) and the host build of the kernels'
+numerical headers (tests/host_harness) against the committed cv2 golden vectors and against cv2 itself."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from tests import util
+from oracle import cv_literal as lit
+from oracle import opencv_replay as rp
+
+G = np.load(os.path.join(util.GOLDEN, "cv2_golden.npz"))
+cv2 = pytest.importorskip("cv2")
+
+
+def test_golden_cv2_version_note():
+    # golden vectors were minted with 4.13.0; a different binary is allowed but flagged in the report
+    assert str(G["cv2_version"]).split(".")[0] == cv2.__version__.split(".")[0]
+
+
+@pytest.mark.parametrize("i", [0, 1, 2])
+def test_hamming_numpy_restatement_vs_golden(i):
+    d0, d1 = G[f"ham{i}_d0"], G[f"ham{i}_d1"]
+    m0, dist, _ = lit.hamming_mutual_numpy(d0, d1, cross_check=True)
+    q = np.nonzero(m0 >= 0)[0]
+    assert np.array_equal(q, G[f"ham{i}_q"])
+    assert np.array_equal(m0[q], G[f"ham{i}_t"])
+    assert np.array_equal(dist[q].astype(np.float32), G[f"ham{i}_dist"])
+    mr, _, _ = lit.hamming_mutual_numpy(d0, d1, cross_check=False, ratio=0.7)
+    assert np.array_equal(mr, G[f"ham{i}_ratio07"])
+
+
+def test_hamming_tie_rules():
+    """All-identical descriptors: query -> lowest train, train -> lowest query, keep mutual."""
+    d = np.zeros((3, 32), np.uint8)
+    q, t, dist = lit.bf_hamming_match(d, d)
+    assert q.tolist() == [0] and t.tolist() == [0] and dist.tolist() == [0.0]
+    m0, _, _ = lit.hamming_mutual_numpy(d, d)
+    assert m0.tolist() == [0, -1, -1]
+
+
+def test_orbslam_swar_popcount_known_answer():
+    """ORB_SLAM3/src/ORBmatcher.cc:2058-2074 (SWAR popcount over 8 x 32 bit) equals the table popcount."""
+    rng = np.random.default_rng(5)
+    a = rng.integers(0, 2**32, (50, 8), dtype=np.uint64).astype(np.uint32)
+    b = rng.integers(0, 2**32, (50, 8), dtype=np.uint64).astype(np.uint32)
+    v = a ^ b
+    v = v - ((v >> 1) & 0x55555555)
+    v = (v & 0x33333333) + ((v >> 2) & 0x33333333)
+    swar = ((((v + (v >> 4)) & 0xF0F0F0F).astype(np.uint64) * 0x1010101) & 0xFFFFFFFF) >> 24
+    ref = lit.hamming_matrix(a.view(np.uint8).reshape(50, 32), b.view(np.uint8).reshape(50, 32))
+    assert np.array_equal(swar.sum(1).astype(np.int64), np.diag(ref))
+
+
+def test_rng_matches_cv2():
+    cv2.setRNGSeed(12345)
+    got = np.zeros((8, 1), np.int32)
+    cv2.randu(got, 0, 1000)
+    r = rp.CvRNG(12345)
+    assert [r.uniform(0, 1000) for _ in range(8)] == got.ravel().tolist()
+
+
+def test_sampler_host_harness_equals_replay():
+    hh = util.host_harness()
+    for count in (6, 17, 1000):
+        out = np.zeros((200, 5), np.int32)
+        hh.hh_ransac_subsets(count, 200, util.vp(out))
+        assert np.array_equal(out, rp.ransac_subsets(count, 200))
+
+
+def test_update_num_iters_host_equals_replay():
+    hh = util.host_harness()
+    for ep in (0.0, 0.1, 0.37, 0.5, 0.9, 1.0):
+        for p in (0.99, 0.999):
+            assert hh.hh_update_num_iters(p, ep, 5, 1000) == rp.ransac_update_num_iters(p, ep, 5, 1000)
+
+
+def test_five_point_host_vs_cv2_candidates():
+    """findEssentialMat on exactly 5 points returns every candidate in solver order."""
+    hh = util.host_harness()
+    worst = 0.0
+    for seed in range(60):
+        p0, p1, _, _, _ = util.two_view(5, 1000 + seed, outliers=0.0)
+        E, _ = cv2.findEssentialMat(p0, p1, focal=util.FOCAL, pp=util.PP, method=cv2.RANSAC, prob=0.999,
+                                    threshold=1.0)
+        q1, q2 = util.normalise(p0), util.normalise(p1)
+        models = np.zeros(90)
+        n = hh.hh_five_point(util.vp(q1), util.vp(q2), util.vp(models))
+        assert n == (0 if E is None else E.shape[0] // 3), seed
+        if n:
+            worst = max(worst, float(np.abs(models[:9 * n].reshape(-1, 3) - E).max()))
+    assert worst < 1e-4, worst  # ill-conditioned subsets amplify the last-bit differences of libm
+
+
+def _hh_find_essential(p0, p1, max_iters=1000):
+    hh = util.host_harness()
+    hh.hh_find_essential.restype = C.c_int
+    hh.hh_find_essential.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double,
+                                     C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+    n = p0.shape[0]
+    E = np.zeros(9)
+    mask = np.zeros(n, np.uint8)
+    it = C.c_int(0)
+    c = hh.hh_find_essential(util.vp(p0), util.vp(p1), n, util.FOCAL, util.PP[0], util.PP[1], 0.999, 1.0,
+                             max_iters, util.vp(E), util.vp(mask), C.byref(it))
+    return c, E.reshape(3, 3), mask, it.value
+
+
+def _hh_recover_pose(E, p0, p1):
+    hh = util.host_harness()
+    hh.hh_recover_pose.restype = C.c_int
+    hh.hh_recover_pose.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_double, C.c_double,
+                                   C.c_double, C.c_double, C.c_void_p, C.c_void_p, C.c_void_p]
+    n = p0.shape[0]
+    R = np.zeros(9)
+    t = np.zeros(3)
+    mask = np.zeros(n, np.uint8)
+    E = np.ascontiguousarray(E, dtype=np.float64)
+    ng = hh.hh_recover_pose(util.vp(E), util.vp(p0), util.vp(p1), n, util.FOCAL, util.PP[0], util.PP[1], 50.0,
+                            util.vp(R), util.vp(t), util.vp(mask))
+    return ng, R.reshape(3, 3), t, mask
+
+
+@pytest.mark.parametrize("i", [0, 1, 2])
+def test_essential_host_code_vs_golden(i):
+    p0, p1 = G[f"ess{i}_p0"], G[f"ess{i}_p1"]
+    c, E, mask, _ = _hh_find_essential(p0, p1)
+    assert np.array_equal(mask, G[f"ess{i}_mask"].ravel())
+    assert c == int(G[f"ess{i}_mask"].sum())
+    assert np.abs(E - G[f"ess{i}_E"]).max() < 1e-7
+    ng, R, t, pm = _hh_recover_pose(G[f"ess{i}_E"], p0, p1)
+    assert ng == int(G[f"ess{i}_ngood"])
+    assert np.array_equal(pm, G[f"ess{i}_pmask"].ravel())
+    assert lit.angle_error_mat(R, G[f"ess{i}_R"]) < 1e-4
+    assert lit.angle_error_vec(t, G[f"ess{i}_t"].ravel()) < 1e-4
+
+
+def test_essential_python_replay_vs_golden():
+    """oracle/opencv_replay.py (pure NumPy restatement) reproduces cv2's mask on a small case."""
+    p0, p1 = G["ess0_p0"], G["ess0_p1"]
+    r = rp.find_essential_ransac(p0, p1, util.FOCAL, util.PP)
+    assert np.array_equal(r["mask"], G["ess0_mask"].ravel())
+    assert np.abs(r["E"] - G["ess0_E"]).max() < 1e-6
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_essential_host_code_vs_cv2_live(seed):
+    n = [60, 300, 1200][seed % 3]
+    p0, p1, _, _, _ = util.two_view(n, 5000 + seed, outliers=[0.1, 0.3, 0.5][(seed // 3) % 3])
+    E, mask = lit.find_essential(p0, p1)
+    c, Eo, mo, _ = _hh_find_essential(p0, p1)
+    assert np.array_equal(mo, mask.ravel())
+    ng_cv, R, t, pm = lit.recover_pose(E, p0, p1)
+    ng, Ro, to, pmo = _hh_recover_pose(E, p0, p1)
+    assert ng == ng_cv and np.array_equal(pmo, pm.ravel())
+    assert np.abs(Ro - R).max() < 1e-9 and np.abs(to - t.ravel()).max() < 1e-9
+
+
+def test_backproject_oracle_vs_golden():
+    p3, valid = lit.backproject(G["bp_kp"], G["bp_disp"])
+    assert np.array_equal(valid, G["bp_valid"])
+    assert np.array_equal(p3, G["bp_p3"])
+    # the clean-up rules of stereo_slam.py:120-121
+    d = G["bp_disp"]
+    z = p3[:, 2]
+    c = np.float32(lit.K0[0, 0] * lit.BASELINE)
+    assert np.all(z[(d == 0) | (d == -1)] == c / np.float32(0.1))
+
+
+def test_degenerate_inputs_of_cv2():
+    """the defined outputs the C ABI mirrors."""
+    p = np.zeros((4, 2), np.float32)
+    E, mask = cv2.findEssentialMat(p, p, focal=1.0, pp=(0., 0.), method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    assert E is None and mask is None
+    assert cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True).match(np.zeros((0, 32), np.uint8),
+                                                                   np.zeros((3, 32), np.uint8)) == ()
