@@ -1,0 +1,132 @@
+"""GPU parity: A2 (Hamming), A1 (float, exact-fp32 kernel), A3 (gather) through the C ABI vs the oracle."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import util
+from oracle import cv_literal as lit
+
+pytestmark = pytest.mark.gpu
+G = np.load(os.path.join(util.GOLDEN, "cv2_golden.npz"))
+
+
+@pytest.fixture(scope="module")
+def fsb():
+    import torch
+    assert torch.cuda.is_available()
+    from forest_slam_b200 import api
+    return api
+
+
+def _matches_to_arrays(ms):
+    return (np.array([m.queryIdx for m in ms], np.int32), np.array([m.trainIdx for m in ms], np.int32),
+            np.array([m.distance for m in ms], np.float32))
+
+
+@pytest.mark.parametrize("i", [0, 1, 2])
+def test_hamming_golden(fsb, i):
+    ms = fsb.BFMatcher(fsb.NORM_HAMMING, crossCheck=True).match(G[f"ham{i}_d0"], G[f"ham{i}_d1"])
+    q, t, d = _matches_to_arrays(ms)
+    assert np.array_equal(q, G[f"ham{i}_q"]) and np.array_equal(t, G[f"ham{i}_t"])
+    assert np.array_equal(d, G[f"ham{i}_dist"])
+    mr = fsb.BFMatcher(fsb.NORM_HAMMING).ratioMatch(G[f"ham{i}_d0"], G[f"ham{i}_d1"], 0.7)
+    got = np.full(G[f"ham{i}_d0"].shape[0], -1, np.int32)
+    for m in mr:
+        got[m.queryIdx] = m.trainIdx
+    assert np.array_equal(got, G[f"ham{i}_ratio07"])
+
+
+@pytest.mark.parametrize("n0,n1,seed", [(2000, 2000, 1), (2048, 1777, 2), (1, 1, 3), (31, 1000, 4), (513, 2, 5)])
+def test_hamming_vs_cv2(fsb, n0, n1, seed):
+    d0, d1 = util.binary_descriptors(n0, n1, seed)
+    q, t, d = lit.bf_hamming_match(d0, d1)
+    gq, gt, gd = _matches_to_arrays(fsb.BFMatcher(fsb.NORM_HAMMING, crossCheck=True).match(d0, d1))
+    assert np.array_equal(q, gq) and np.array_equal(t, gt) and np.array_equal(d, gd)
+
+
+def test_hamming_ties_and_empty(fsb):
+    z = np.zeros((3, 32), np.uint8)
+    ms = fsb.BFMatcher(fsb.NORM_HAMMING, crossCheck=True).match(z, z)
+    assert [(m.queryIdx, m.trainIdx, m.distance) for m in ms] == [(0, 0, 0.0)]
+    assert fsb.BFMatcher(fsb.NORM_HAMMING, crossCheck=True).match(np.zeros((0, 32), np.uint8), z) == ()
+    # heavy ties: few distinct descriptors
+    rng = np.random.default_rng(9)
+    pool = rng.integers(0, 256, (7, 32), dtype=np.uint8)
+    d0, d1 = pool[rng.integers(0, 7, 300)], pool[rng.integers(0, 7, 333)]
+    q, t, d = lit.bf_hamming_match(d0, d1)
+    gq, gt, gd = _matches_to_arrays(fsb.BFMatcher(fsb.NORM_HAMMING, crossCheck=True).match(d0, d1))
+    assert np.array_equal(q, gq) and np.array_equal(t, gt) and np.array_equal(d, gd)
+
+
+def test_hamming_batch_ragged(fsb):
+    """A frame bank with ragged counts, several pairs in one launch, equals pair-by-pair cv2."""
+    import torch
+    rng = np.random.default_rng(11)
+    counts = [700, 512, 1, 0, 655]
+    n_max = 704
+    bank = np.zeros((5, n_max, 32), np.uint8)
+    for f, c in enumerate(counts):
+        bank[f, :c] = rng.integers(0, 256, (c, 32), dtype=np.uint8)
+    bank[1, :300] = bank[0, 100:400] ^ np.packbits(rng.random((300, 256)) < 0.05, axis=1)
+    bank[4, :500] = bank[1, :500] ^ np.packbits(rng.random((500, 256)) < 0.05, axis=1)
+    pa, pb = [0, 1, 1, 2, 3, 0, 4], [1, 4, 0, 0, 1, 3, 4]
+    r = fsb.hamming_match_batch(torch.from_numpy(bank).cuda(), torch.tensor(counts, dtype=torch.int32).cuda(),
+                                pa, pb, cross_check=True)
+    m0 = r["matches0"].cpu().numpy()
+    m1 = r["matches1"].cpu().numpy()
+    nm = r["n_matches"].cpu().numpy()
+    for p, (a, b) in enumerate(zip(pa, pb)):
+        ref, _, _ = lit.hamming_mutual_numpy(bank[a, :counts[a]], bank[b, :counts[b]])
+        assert np.array_equal(m0[p, :counts[a]], ref), p
+        assert np.all(m0[p, counts[a]:] == -1)
+        assert nm[p] == int((ref >= 0).sum())
+        inv = np.full(n_max, -1, np.int32)
+        inv[ref[ref >= 0]] = np.nonzero(ref >= 0)[0]
+        assert np.array_equal(m1[p], inv)
+
+
+@pytest.mark.parametrize("n0,n1,seed,thr,ratio", [(1024, 1024, 1, None, None), (1000, 777, 2, 0.2, None),
+                                                  (640, 1100, 3, None, 0.8), (1, 5, 4, None, None),
+                                                  (4096, 4096, 5, 0.5, 0.9)])
+@pytest.mark.parametrize("exact", [True])
+def test_float_mutual_nn(fsb, n0, n1, seed, thr, ratio, exact):
+    d0, d1 = util.float_descriptors(n0, n1, seed)
+    ref = lit.float_mutual_nn(d0, d1, threshold=thr, ratio=ratio)
+    got = fsb.match_mutual_nn(d0, d1, threshold=thr, ratio=ratio, exact_fp32=exact)
+    keep = ~ref["ambiguous0"]
+    assert keep.mean() > 0.95
+    assert np.array_equal(got["matches0"][keep], ref["matches0"][keep])
+    ok = ref["matches0"] >= 0
+    assert np.allclose(got["matching_scores0"][ok & keep], ref["score0"][ok & keep], atol=2e-6)
+    # matches1 is the inverse permutation of matches0 (superglue.py:271-278)
+    m0, m1 = got["matches0"], got["matches1"]
+    q = np.nonzero(m0 >= 0)[0]
+    assert np.array_equal(m1[m0[q]], q)
+    assert (m1 >= 0).sum() == q.size
+
+
+def test_float_zero_keypoints(fsb):
+    r = fsb.match_mutual_nn(np.zeros((256, 0), np.float32), np.zeros((256, 7), np.float32))
+    assert r["matches0"].shape == (0,) and np.all(r["matches1"] == -1)
+
+
+def test_gather_matches(fsb):
+    import torch
+    rng = np.random.default_rng(21)
+    n_max, counts = 900, [900, 640, 0]
+    kp = rng.uniform(0, 960, (3, n_max, 2)).astype(np.float32)
+    pa, pb = [0, 1, 2, 0], [1, 0, 0, 2]
+    m = np.full((4, n_max), -1, np.int32)
+    for p, (a, b) in enumerate(zip(pa, pb)):
+        if counts[a] and counts[b]:
+            k = min(counts[a], counts[b]) // 2
+            m[p, rng.choice(counts[a], k, replace=False)] = rng.choice(counts[b], k, replace=False)
+    r = fsb.gather_matches_batch(torch.from_numpy(kp).cuda(), torch.tensor(counts, dtype=torch.int32).cuda(), pa, pb,
+                                 torch.from_numpy(m).cuda())
+    nc = r["n_corr"].cpu().numpy()
+    for p, (a, b) in enumerate(zip(pa, pb)):
+        mk0, mk1 = lit.gather_matches(kp[a, :counts[a]], kp[b], m[p, :counts[a]])
+        assert nc[p] == mk0.shape[0]
+        assert np.array_equal(r["mkpts0"][p, :nc[p]].cpu().numpy(), mk0)
+        assert np.array_equal(r["mkpts1"][p, :nc[p]].cpu().numpy(), mk1)
