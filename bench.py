@@ -1,0 +1,385 @@
+#!/usr/bin/env python
+"""bench.py — frame-pairs/s of the Forest-SLAM matching + pose hot path on N B200s, next to the host-CPU reference.
+
+Contract (driver): `python bench.py --gpus N --steps K --warmup W [--impl reference]` prints ONE JSON line on rank 0.
+A step = one pass of the hot path over one batch of synthetic frame pairs (BASELINE.json configs[1]: mono_slam.py
+temporal matching + essential-matrix RANSAC + recoverPose at 2048 keypoints/frame; `--workload stereo` runs the
+stereo_slam.py path: Hamming match + depth back-projection + PnP RANSAC at 2000 keypoints/frame).
+value   = pairs/s with the frame bank resident in HBM, CUDA events, max over ranks;
+e2e     = the same through the public batched API with HOST (pinned) buffers: H2D of the frame bank and D2H of the
+          per-pair result records inside the timed region;
+roofline= the dominant kernel's algorithmic work / its CUDA-event time inside the timed steps vs MEASURED_PEAKS.json;
+cpu_baseline = the reference's own cv2/torch-CPU calls (oracle/cv_literal.py) timed on a bounded sample on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "frame-pairs/sec (match+RANSAC+triangulate)"
+UNIT = "frame-pairs/s"
+LN_THRESH = math.log(0.2)  # superglue.py:275 exp(score) > 0.2 on the scaled score
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="mono", choices=["mono", "stereo"])
+    ap.add_argument("--pairs", type=int, default=128, help="frame pairs per step per GPU")
+    ap.add_argument("--kpts", type=int, default=0, help="keypoints per frame (default 2048 mono / 2000 stereo)")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="pairs timed for cpu_baseline (0 = auto)")
+    ap.add_argument("--exact-fp32", action="store_true", help="CUDA-core fp32 matcher instead of tcgen05")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------ workload
+def make_workload(args, rank: int):
+    """Seeded synthetic sequence (procedural forest): `pairs + 1` frames of `kpts` keypoints for this rank."""
+    from forest_slam_b200 import synth
+    n_kpts = args.kpts or (2048 if args.workload == "mono" else 2000)
+    world = synth.make_world(synth.SEED0)
+    frames = synth.make_sequence(args.pairs + 1, n_kpts, seed=synth.SEED0 + 1000 * rank, world=world)
+    kpts, dbin, df32, disp, counts = synth.stack_frames(frames)
+    return {"frames": frames, "kpts": kpts, "desc_bin": dbin, "desc_f32": df32, "disparity": disp, "counts": counts,
+            "n_kpts": n_kpts}
+
+
+def config_dict(args, wl, world_size):
+    name = ("mono_slam.py temporal matching (float 256-d mutual-NN) + essential-matrix RANSAC + recoverPose"
+            if args.workload == "mono" else
+            "stereo_slam.py temporal matching (256-bit Hamming crossCheck) + depth back-projection + PnP RANSAC")
+    return {"workload": name, "kpts_per_frame": int(wl["n_kpts"]), "pairs_per_step_per_gpu": int(args.pairs),
+            "image": "960x600", "sharding": f"frame-pair index over {world_size} rank(s), one all_gather of records",
+            "l2": "L2 flushed (256 MB write) between timed iterations; frame bank per step %.0f MB" % (
+                bank_bytes(args, wl) / 1e6)}
+
+
+def bank_bytes(args, wl):
+    F = args.pairs + 1
+    n = wl["n_kpts"]
+    per = n * 8 + (n * 256 * 4 if args.workload == "mono" else n * 32 + n * 4)
+    return F * per
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 6:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU reference
+def _cpu_worker(job):
+    import cv2
+    cv2.setNumThreads(1)
+    import torch
+    torch.set_num_threads(1)
+    from oracle import cv_literal as lit
+    kind, a = job
+    t0 = time.perf_counter()
+    if kind == "mono":
+        lit.mono_frame_pair(*a)
+    else:
+        lit.stereo_frame_pair(*a)
+    return time.perf_counter() - t0
+
+
+def cpu_reference(args, wl, n_sample: int, procs: int):
+    """The reference's own CPU implementation of the path (oracle/cv_literal.py = the literal cv2 / torch calls of
+    mono_slam.py:100-118 / stereo_slam.py:232-306) over `n_sample` frame pairs, data-parallel over `procs` processes
+    with one library thread each (findEssentialMat / recoverPose / solvePnPRansac are single-threaded in OpenCV)."""
+    fr = wl["frames"]
+    n_sample = max(1, min(n_sample, len(fr) - 1))
+    jobs = []
+    for i in range(n_sample):
+        a, b = fr[i], fr[i + 1]
+        if args.workload == "mono":
+            jobs.append(("mono", (a.kpts, a.desc_f32, b.kpts, b.desc_f32)))
+        else:
+            jobs.append(("stereo", (a.kpts, a.desc_bin, a.disparity, b.kpts, b.desc_bin)))
+    if procs <= 1:
+        t0 = time.perf_counter()
+        for j in jobs:
+            _cpu_worker(j)
+        dt = time.perf_counter() - t0
+    else:
+        import multiprocessing as mp
+        ctx = mp.get_context("spawn")  # the parent holds a CUDA context and OpenMP pools: never fork it
+        with ctx.Pool(procs) as pool:
+            pool.map(_cpu_worker, jobs[:procs])  # warm the workers (imports, page-in)
+            t0 = time.perf_counter()
+            pool.map(_cpu_worker, jobs, chunksize=1)
+            dt = time.perf_counter() - t0
+    return n_sample / dt, dt, n_sample
+
+
+def run_reference(args):
+    """`--impl reference`: the reference's CPU path on the box's host cores, same config / metric / unit."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    wl = make_workload(args, 0)
+    procs = os.cpu_count() or 1
+    for _ in range(max(args.warmup, 0)):
+        cpu_reference(args, wl, min(args.pairs, 2 * procs), procs)
+    tot_pairs, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        _, dt, n = cpu_reference(args, wl, args.pairs, procs)
+        tot_pairs += n
+        tot_t += dt
+    value = tot_pairs / tot_t
+    import cv2
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64 solvers / f32 residuals", "data": "synthetic (procedural forest, seeded)",
+            "config": config_dict(args, wl, 1),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "reference",
+                             "sample": f"{args.pairs} frame pairs per step, {procs} processes x 1 library thread, "
+                                       f"cv2 {cv2.__version__} + torch CPU (oracle/cv_literal.py literal calls)"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ B200 arm
+def stage_work(args, wl, res, stage: str):
+    """Algorithmic work of one step of `stage` (SURVEY §8d figures): (bound, amount, unit)."""
+    P, n = args.pairs, wl["n_kpts"]
+    k = float(res["n_matches"].float().mean().item()) if "n_matches" in res else 0.0
+    it = float(res["iters"].float().mean().item()) if "iters" in res else 0.0
+    if stage == "match" and args.workload == "mono":
+        return "tensor", P * 2.0 * n * n * 256, "TFLOP/s"
+    if stage == "match":
+        return "hbm", P * ((n + n) * 32.0 + n * 12.0), "GB/s"
+    if stage == "essential_ransac":
+        return "hbm", P * (k * 16.0 + it * (20.0 + 72.0 + 4.0) + k + 72.0), "GB/s"
+    if stage == "pnp_ransac":
+        return "hbm", P * (k * 20.0 + it * (20.0 + 48.0 + 4.0) + k * 5.0 + 48.0), "GB/s"
+    if stage == "recover_pose":
+        return "hbm", P * (k * 16.0 + k + 72.0 + 96.0), "GB/s"
+    if stage == "triangulate":
+        return "hbm", P * k * (12.0 + 8.0 + 20.0), "GB/s"
+    return "hbm", P * k * (4.0 + 32.0), "GB/s"  # gather: matches in, two point pairs out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from forest_slam_b200 import _lib, sequence as seq
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: forest_slam_b200 has no CPU path")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    wl = make_workload(args, rank)
+    P = args.pairs
+    pa = torch.arange(0, P, dtype=torch.int32, device=dev)
+    pb = pa + 1
+    host = {"kpts": torch.from_numpy(wl["kpts"]).pin_memory(), "counts": torch.from_numpy(wl["counts"]).pin_memory()}
+    if args.workload == "mono":
+        host["desc_f32"] = torch.from_numpy(wl["desc_f32"]).pin_memory()
+    else:
+        host["desc_bin"] = torch.from_numpy(wl["desc_bin"]).pin_memory()
+        host["disparity"] = torch.from_numpy(wl["disparity"]).pin_memory()
+    devbuf = {k: torch.empty_like(v, device=dev) for k, v in host.items()}
+    h2d_bytes = sum(v.numel() * v.element_size() for v in host.values())
+
+    def upload():
+        for k, v in host.items():
+            devbuf[k].copy_(v, non_blocking=True)
+        return seq.FrameBank(kpts=devbuf["kpts"], counts=devbuf["counts"], desc_f32=devbuf.get("desc_f32"),
+                             desc_bin=devbuf.get("desc_bin"), disparity=devbuf.get("disparity"))
+
+    def step(bank, timer=None):
+        if args.workload == "mono":
+            res = seq.mono_pairs(bank, pa, pb, descriptor="float", scale=0.0625, threshold=LN_THRESH,
+                                 exact_fp32=args.exact_fp32, timer=timer)
+        else:
+            res = seq.stereo_pairs(bank, pa, pb, descriptor="binary", timer=timer)
+        rec = seq.pack_records(res)
+        allrec = seq.gather_records(rec, P * world)
+        return res, allrec
+
+    rec_host = torch.empty((P * world, seq.RECORD_F64), dtype=torch.float64).pin_memory()
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    bank = upload()
+    torch.cuda.synchronize()
+    for _ in range(max(args.warmup, 3)):
+        step(bank)
+    # ---- device-resident timing (value)
+    timer = seq.StageTimer()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    l0 = lib.fs_launch_count()
+    wall0 = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()  # L2 flush between timed iterations (outside the per-step events)
+        ev[i][0].record()
+        res, allrec = step(bank, timer)
+        ev[i][1].record()
+    barrier()
+    wall = time.perf_counter() - wall0
+    launches = lib.fs_launch_count() - l0
+    clk = clocks.stop()
+    t_dev = sum(a.elapsed_time(b) for a, b in ev) / 1e3
+    # ---- end-to-end timing through the public API with host buffers (e2e)
+    for _ in range(2):
+        b2 = upload()
+        _, ar = step(b2)
+        rec_host.copy_(ar, non_blocking=True)
+    ev2 = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    for i in range(args.steps):
+        flush.zero_()
+        ev2[i][0].record()
+        b2 = upload()
+        _, ar = step(b2)
+        rec_host.copy_(ar, non_blocking=True)
+        ev2[i][1].record()
+    barrier()
+    t_e2e = sum(a.elapsed_time(b) for a, b in ev2) / 1e3
+    tt = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    t_dev, t_e2e = float(tt[0]), float(tt[1])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    total_pairs = P * world * args.steps
+    value = total_pairs / t_dev
+    stages = timer.totals_ms()
+    dom = max(stages, key=stages.get)
+    bound, work, unit = stage_work(args, wl, res, dom)
+    peaks = {}
+    pk_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    peak_src = "measured (MEASURED_PEAKS.json)"
+    if os.path.exists(pk_path):
+        peaks = json.load(open(pk_path))
+    else:
+        peaks = {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0}
+        peak_src = "fallback (B200_PROFILING.md)"
+    dom_s = stages[dom] / 1e3 / args.steps
+    if bound == "tensor":
+        achieved, peak = work / dom_s / 1e12, float(peaks.get("bf16_tflops_sustained", 1400.0))
+    else:
+        achieved, peak = work / dom_s / 1e9, float(peaks.get("hbm_gbs", 6650.0))
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * t_dev / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16x3-split tensor-core scores + f64 solvers / f32 residuals" if (
+                args.workload == "mono" and not args.exact_fp32) else "u8/f32 + f64 solvers / f32 residuals",
+            "data": "synthetic (procedural forest, seeded)", "config": config_dict(args, wl, world),
+            "clocks": clk,
+            "e2e": {"value": total_pairs / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes),
+                    "d2h_bytes_per_step": int(rec_host.numel() * 8)},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": dom, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
+                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "stage_ms_per_step": {k: v / args.steps for k, v in stages.items()}},
+            "wall_s": wall,
+            "stats": {"mean_matches": float(res["n_matches"].float().mean()),
+                      "mean_inliers": float(res["n_inliers"].float().mean()),
+                      "mean_iters": float(res["iters"].float().mean()),
+                      "ok_pairs": int((res["status"] == 0).sum())}}
+    if world == 1 and not args.no_cpu_baseline:
+        procs = os.cpu_count() or 1
+        n_s = args.cpu_sample or min(args.pairs, 8 * procs)
+        import cv2
+        v, dt, n = cpu_reference(args, wl, n_s, procs)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": procs, "kind": "reference",
+                                "sample": f"{n} frame pairs of this workload in {dt:.1f} s, {procs} processes x 1 "
+                                          f"library thread, cv2 {cv2.__version__} + torch CPU literal calls"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -29,6 +29,7 @@ SIGNATURES = {
     "fs_last_error_string": (C.c_char_p, []),
     "fs_status_string": (C.c_char_p, [C.c_int]),
     "fs_device_sm_count": (C.c_int, []),
+    "fs_launch_count": (C.c_longlong, []),
     "fs_hamming_match_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fs_hamming_match": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_int, C.c_float,
                                    ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),

@@ -1,5 +1,6 @@
 // common.cu — error strings, version, device queries for the C ABI (include/forestslam_b200.h).
 #include <stdarg.h>
+#include <atomic>
 #include "common.cuh"
 
 namespace fs {
@@ -12,6 +13,10 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
 }
+
+static std::atomic<long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
+long long launches() { return g_launches.load(std::memory_order_relaxed); }
 
 int sm_count() {
     static int cached = 0;
@@ -43,5 +48,7 @@ const char* fs_status_string(int s) {
 }
 
 int fs_device_sm_count(void) { return fs::sm_count(); }
+
+long long fs_launch_count(void) { return fs::launches(); }
 
 }  // extern "C"

@@ -27,6 +27,7 @@ inline int check_cuda(cudaError_t e, const char* what) {
 
 #define FS_LAUNCH_CHECK(name)                                 \
     do {                                                      \
+        fs::count_launch();                                   \
         int _s = fs::check_cuda(cudaGetLastError(), name);    \
         if (_s != FS_OK) return _s;                           \
     } while (0)
@@ -42,6 +43,7 @@ inline int check_cuda(cudaError_t e, const char* what) {
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 int sm_count();
+void count_launch();  // every kernel launch of the library bumps fs_launch_count()
 
 // carve a workspace pointer
 struct Carver {

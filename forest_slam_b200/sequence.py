@@ -1,0 +1,176 @@
+"""Batched drivers of the hot path: what the frame loops of mono_slam.py:85-182 and stereo_slam.py:177-345 do per
+frame pair, run for a whole list of frame pairs in a handful of launches, and sharded by frame-pair index across the
+ranks of a torch.distributed job (one process per GPU) with ONE gather of fixed-size result records at the end
+(the path has no other cross-GPU dependency).
+
+Everything here enqueues CUDA work through the C ABI (api.py); there is no CPU path.
+"""
+from __future__ import annotations
+
+import dataclasses
+from typing import Dict, Optional
+
+import torch
+
+from . import api
+from .api import ForestCamera
+
+RECORD_F64 = 20  # n_matches, n_inliers, status, n_good, R[9], t[3], pad -> 20 doubles = 160 B per frame pair
+
+
+@dataclasses.dataclass
+class FrameBank:
+    """Device-resident frame bank (SURVEY.md §8a 'types on the path'): everything the hot path reads."""
+    kpts: torch.Tensor                      # [F, n_max, 2] f32 pixels
+    counts: torch.Tensor                    # [F] i32
+    desc_f32: Optional[torch.Tensor] = None  # [F, 256, n_max] f32 (SuperPoint layout)
+    desc_bin: Optional[torch.Tensor] = None  # [F, n_max, 32] u8 (ORB layout)
+    disparity: Optional[torch.Tensor] = None  # [F, n_max] f32 per-keypoint disparity (uL - uR)
+    operands: Optional[torch.Tensor] = None  # [F, n_max, 512] bf16 split operands of the tensor-core matcher
+
+    @staticmethod
+    def from_numpy(kpts, counts, desc_f32=None, desc_bin=None, disparity=None, device="cuda") -> "FrameBank":
+        def dev(a, dt):
+            return None if a is None else torch.as_tensor(a, dtype=dt).to(device, non_blocking=True).contiguous()
+        return FrameBank(dev(kpts, torch.float32), dev(counts, torch.int32), dev(desc_f32, torch.float32),
+                         dev(desc_bin, torch.uint8), dev(disparity, torch.float32))
+
+
+def shard_pairs(n_pairs: int, rank: int, world: int) -> torch.Tensor:
+    """Pair indices owned by `rank`: i mod world == rank (balances varying correspondence counts)."""
+    return torch.arange(rank, n_pairs, world, dtype=torch.int64)
+
+
+class StageTimer:
+    """Optional CUDA-event bracket around every stage of a batched driver (bench.py reads it for the roofline).
+    Events are recorded on torch's current stream — the stream every launch of api.py is enqueued on."""
+
+    def __init__(self):
+        self.spans = []  # (name, start_event, end_event)
+
+    def run(self, name, fn):
+        a = torch.cuda.Event(enable_timing=True)
+        b = torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        self.spans.append((name, a, b))
+        return out
+
+    def totals_ms(self) -> Dict[str, float]:
+        tot: Dict[str, float] = {}
+        for name, a, b in self.spans:
+            tot[name] = tot.get(name, 0.0) + a.elapsed_time(b)
+        return tot
+
+
+def _run(timer, name, fn):
+    return fn() if timer is None else timer.run(name, fn)
+
+
+def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp32: bool, scale: float = 1.0):
+    if descriptor == "float":
+        if bank.desc_f32 is None and bank.operands is None:
+            raise ValueError("the frame bank holds no float descriptors")
+        r = api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale, threshold=threshold, ratio=ratio,
+                                  operands=bank.operands, exact_fp32=exact_fp32)
+    elif descriptor == "binary":
+        if bank.desc_bin is None:
+            raise ValueError("the frame bank holds no binary descriptors")
+        r = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, ratio=ratio,
+                                    want_matches1=False)
+    else:
+        raise ValueError("descriptor must be 'float' or 'binary'")
+    return r
+
+
+def mono_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "float", camera: ForestCamera = ForestCamera(),
+               threshold: Optional[float] = None, ratio: Optional[float] = None, prob: float = 0.999,
+               ransac_threshold: float = 1.0, max_iters: int = 1000, exact_fp32: bool = False, scale: float = 1.0,
+               timer: Optional[StageTimer] = None) -> Dict[str, torch.Tensor]:
+    """mono_slam.py:100-118 for every (pair_a[i], pair_b[i]): match -> gather -> findEssentialMat(RANSAC) -> recoverPose.
+    The single `focal` for both axes and recoverPose without the RANSAC mask are the reference's behaviour."""
+    dev = bank.kpts.device
+    pa = api._to_cuda(pair_a, torch.int32, dev)
+    pb = api._to_cuda(pair_b, torch.int32, dev)
+    m = _run(timer, "match", lambda: _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale))
+    g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
+    pp = (camera.cx, camera.cy)
+    e = _run(timer, "essential_ransac",
+             lambda: api.find_essential_batch(g["mkpts0"], g["mkpts1"], g["n_corr"], focal=camera.fx, pp=pp, prob=prob,
+                                              threshold=ransac_threshold, max_iters=max_iters))
+    r = _run(timer, "recover_pose",
+             lambda: api.recover_pose_batch(e["E"], g["mkpts0"], g["mkpts1"], g["n_corr"], focal=camera.fx, pp=pp,
+                                            status=e["status"]))
+    return {"matches0": m["matches0"], "n_matches": g["n_corr"], "mkpts0": g["mkpts0"], "mkpts1": g["mkpts1"],
+            "E": e["E"], "inlier_mask": e["mask"], "n_inliers": e["n_inliers"], "status": e["status"],
+            "iters": e["iters"], "R": r["R"], "t": r["t"], "pose_mask": r["mask"], "n_good": r["n_good"]}
+
+
+def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary", camera: ForestCamera = ForestCamera(),
+                 threshold: Optional[float] = None, ratio: Optional[float] = None, reproj_error: float = 1.0,
+                 confidence: float = 0.99, max_iters: int = 1000, exact_fp32: bool = False, scale: float = 1.0,
+                 timer: Optional[StageTimer] = None) -> Dict[str, torch.Tensor]:
+    """stereo_slam.py:210-306 for every pair: temporal match (left) -> gather -> depth back-projection of the previous
+    frame's keypoints + joint depth filter -> solvePnPRansac (>= 6 gate) -> Rodrigues."""
+    if bank.disparity is None:
+        raise ValueError("the frame bank holds no disparity")
+    dev = bank.kpts.device
+    pa = api._to_cuda(pair_a, torch.int32, dev)
+    pb = api._to_cuda(pair_b, torch.int32, dev)
+    m = _run(timer, "match", lambda: _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale))
+    g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
+    # per-correspondence disparity of the previous-left keypoint (the reference looks it up in the SGBM map)
+    P, n_max = g["src_idx"].shape
+    disp = torch.gather(bank.disparity.index_select(0, pa.long()), 1, g["src_idx"].clamp_(0, n_max - 1).long())
+    b = _run(timer, "triangulate",
+             lambda: api.backproject_filter_batch(g["mkpts0"], g["mkpts1"], disp, g["n_corr"], camera=camera))
+    s = _run(timer, "pnp_ransac",
+             lambda: api.solve_pnp_ransac_batch(b["points3d"], b["pts2d"], b["n_out"], camera=camera,
+                                                reproj_error=reproj_error, confidence=confidence, max_iters=max_iters,
+                                                min_points=6))
+    R = api.rodrigues_batch(s["rvec"])
+    return {"matches0": m["matches0"], "n_matches": g["n_corr"], "points3d": b["points3d"], "pts2d": b["pts2d"],
+            "n_points": b["n_out"], "rvec": s["rvec"], "tvec": s["tvec"], "R": R, "t": s["tvec"],
+            "inlier_mask": s["mask"], "inlier_idx": s["inlier_idx"], "n_inliers": s["n_inliers"],
+            "status": s["status"], "iters": s["iters"]}
+
+
+def pack_records(res: Dict[str, torch.Tensor]) -> torch.Tensor:
+    """Fixed-size per-pair result record [P, 20] f64: n_matches, n_inliers, status, n_good, R(9), t(3), iters, pad."""
+    P = res["R"].shape[0]
+    rec = torch.zeros((P, RECORD_F64), dtype=torch.float64, device=res["R"].device)
+    rec[:, 0] = res["n_matches"].double()
+    rec[:, 1] = res["n_inliers"].double()
+    rec[:, 2] = res["status"].double()
+    if "n_good" in res:
+        rec[:, 3] = res["n_good"].double()
+    rec[:, 4:13] = res["R"].reshape(P, 9)
+    rec[:, 13:16] = res["t"].reshape(P, 3)
+    rec[:, 16] = res["iters"].double()
+    return rec
+
+
+def gather_records(rec_local: torch.Tensor, n_pairs_total: int) -> torch.Tensor:
+    """The one collective of the path: all ranks' records -> [n_pairs_total, 20] in pair-index order on every rank
+    (NCCL all_gather over NVLink; pair i lives on rank i mod W at slot i // W)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return rec_local
+    W = dist.get_world_size()
+    per = (n_pairs_total + W - 1) // W
+    pad = torch.zeros((per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
+    pad[: rec_local.shape[0]] = rec_local
+    out = torch.empty((W, per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
+    dist.all_gather_into_tensor(out.view(W * per, -1), pad)
+    # [W, per] -> pair index i = slot * W + rank
+    return out.permute(1, 0, 2).reshape(W * per, -1)[:n_pairs_total]
+
+
+def trajectory(records: torch.Tensor) -> torch.Tensor:
+    """T_cum = T_cum @ T_rel over the gathered records (mono_slam.py:115-118, stereo_slam.py:301-306)."""
+    P = records.shape[0]
+    R = records[:, 4:13].reshape(P, 3, 3).contiguous()
+    t = records[:, 13:16].contiguous()
+    status = records[:, 2].to(torch.int32).contiguous()
+    return api.compose_trajectory(R, t, status)

@@ -52,6 +52,8 @@ const char* fs_last_error_string(void);
 const char* fs_status_string(int status);
 /* number of SMs of the current device (grid sizing is done inside the library; exported for benches) */
 int fs_device_sm_count(void);
+/* number of kernels this library has launched in this process so far (bench.py reports the delta) */
+long long fs_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
  * A2  binary descriptor matching — replaces

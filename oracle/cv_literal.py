@@ -214,3 +214,37 @@ def angle_error_vec(v1, v2):
     """SuperGluePretrainedNetwork/models/utils.py:383-385, in radians."""
     n = np.linalg.norm(v1) * np.linalg.norm(v2)
     return float(np.arccos(np.clip(np.dot(v1, v2) / n, -1.0, 1.0)))
+
+
+# ---------------------------------------------------------------------------------------------- timed CPU baseline
+def superglue_match_tail(desc0: np.ndarray, desc1: np.ndarray, match_threshold: float = 0.2):
+    """SuperGluePretrainedNetwork/models/superglue.py:259-260 and :268-278 issued literally with torch on the CPU
+    (the neural steps between them — GNN, Sinkhorn — are out of scope and skipped): dense score contraction,
+    row/column max, mutual check, exp(score) > threshold, -1 fill.  desc [256, N] float32 → matches0 [N0] int64."""
+    import torch
+    mdesc0 = torch.from_numpy(desc0)[None]
+    mdesc1 = torch.from_numpy(desc1)[None]
+    scores = torch.einsum('bdn,bdm->bnm', mdesc0, mdesc1)
+    scores = scores / 256 ** .5
+    max0, max1 = scores.max(2), scores.max(1)
+    indices0, indices1 = max0.indices, max1.indices
+    arange = torch.arange(indices0.shape[1])[None]
+    mutual0 = arange == indices1.gather(1, indices0)
+    zero = scores.new_tensor(0)
+    mscores0 = torch.where(mutual0, max0.values.exp(), zero)
+    valid0 = mutual0 & (mscores0 > match_threshold)
+    indices0 = torch.where(valid0, indices0, indices0.new_tensor(-1))
+    return indices0[0].numpy()
+
+
+def mono_frame_pair(kpts0, desc0, kpts1, desc1):
+    """One iteration of the mono_slam.py loop body restricted to the hot path (mono_slam.py:100-118)."""
+    matches = superglue_match_tail(desc0, desc1)
+    return mono_pair(kpts0, kpts1, matches)
+
+
+def stereo_frame_pair(kpts0, descb0, disp0, kpts1, descb1):
+    """One iteration of the stereo_slam.py loop body restricted to the hot path, ORB/BF variant
+    (stereo_slam.py:232-246, :264-306); the per-keypoint disparity stands in for the SGBM map lookup."""
+    q, t, _ = bf_hamming_match(descb0, descb1)
+    return stereo_pair(kpts0[q], kpts1[t], disp0[q])
