@@ -31,6 +31,10 @@ NORM_L2 = 4       # cv2.NORM_L2
 RANSAC = 8        # cv2.RANSAC
 SOLVEPNP_ITERATIVE = 0
 
+# the tcgen05 float matcher (csrc/float_tc.cu) is selected by default once it is built; the exact-fp32 CUDA-core
+# kernel serves descriptor counts that are not a multiple of 128 and `exact_fp32=True`
+TENSOR_CORE_MATCHER = False
+
 DMatch = collections.namedtuple("DMatch", ["queryIdx", "trainIdx", "distance"])
 
 
@@ -189,7 +193,7 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
     rat = float(ratio) if ratio else 0.0
     nbytes = lib.fs_float_match_workspace_bytes(P, n_max)
     ws = _workspace(nbytes, dev)
-    use_tc = (not exact_fp32) and n_max % 128 == 0
+    use_tc = TENSOR_CORE_MATCHER and (not exact_fp32) and n_max % 128 == 0
     if use_tc:
         if operands is None:
             operands = float_prepare(desc, counts)

@@ -42,6 +42,21 @@ CVM_HD int ransac_update_num_iters(double p, double ep, int model_points, int ma
     return (denom >= 0 || -num >= max_iters * (-denom)) ? max_iters : (int)rint(num / denom);
 }
 
+// core/lapack.cpp defines its own hypot (plain arithmetic, no libm): used by the Jacobi rotations
+CVM_HD double hypot_cv(double a, double b) {
+    a = fabs(a);
+    b = fabs(b);
+    if (a > b) {
+        b /= a;
+        return a * sqrt(1 + b * b);
+    }
+    if (b > 0) {
+        a /= b;
+        return b * sqrt(1 + a * a);
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------ JacobiSVD
 // JacobiSVDImpl_<double> (core/lapack.cpp).  At holds N row vectors of length M (the matrix whose rows
 // are orthogonalised in place), Vt the N x N accumulated rotations, W the singular values.  After the
@@ -74,7 +89,7 @@ CVM_HD void jacobi_svd(double* At, int lda, double* W, double* Vt /* N*N or null
                 for (int k = 0; k < M; k++) p += Ai[k] * Aj[k];
                 if (fabs(p) <= eps * sqrt(a * b)) continue;
                 p *= 2;
-                double beta = a - b, gamma = hypot(p, beta), c, s;
+                double beta = a - b, gamma = hypot_cv(p, beta), c, s;
                 if (beta < 0) {
                     double delta = (gamma - beta) * 0.5;
                     s = sqrt(delta / gamma);
@@ -85,8 +100,8 @@ CVM_HD void jacobi_svd(double* At, int lda, double* W, double* Vt /* N*N or null
                 }
                 a = b = 0;
                 for (int k = 0; k < M; k++) {
-                    double t0 = c * Ai[k] + s * Aj[k];
-                    double t1 = -s * Ai[k] + c * Aj[k];
+                    const double t0 = c * Ai[k] + s * Aj[k];
+                    const double t1 = -s * Ai[k] + c * Aj[k];
                     Ai[k] = t0;
                     Aj[k] = t1;
                     a += t0 * t0;

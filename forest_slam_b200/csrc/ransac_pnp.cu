@@ -2,7 +2,7 @@
 // Scoring: one warp per hypothesis over all 3D-2D correspondences staged in shared memory (SoA), projection
 // with the reference's distortion coefficients in OpenCV's operation order, float32 error <= (float)thr^2.
 #include "common.cuh"
-#include "pnpmath.cuh"
+#include "epnp.cuh"
 
 namespace {
 
@@ -38,7 +38,7 @@ struct PnPStage {
             v[i] = q.y;
         }
     }
-    static size_t bytes(int n_max) { return (size_t)n_max * (3 * sizeof(double) + 2 * sizeof(float)); }
+    __host__ __device__ static size_t bytes(int n_max) { return (size_t)n_max * (3 * sizeof(double) + 2 * sizeof(float)); }
 };
 
 __device__ __forceinline__ int warp_count_reproj(const double* R, const double* t, const cvm::CamD& cam,
@@ -80,6 +80,413 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------ A7 RANSAC
+// One CTA per frame pair, rounds of 32 RANSAC iterations (same structure as k_essential_ransac):
+//   sample : thread 0 replays cv::RNG(2^64-1) (RANSACPointSetRegistrator::getSubset);
+//   solve  : 32 threads, one EPnP-on-5-points each (epnp.cuh) -> model (rvec | tvec) in shared memory;
+//   score  : ONE WARP PER HYPOTHESIS over all correspondences staged in shared memory: projectPoints with the
+//            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, ballot/popc count;
+//   select : thread 0 walks the counts in OpenCV's serial order (strictly greater, adaptive iteration cap).
+constexpr int PR_THREADS = 256;
+constexpr int PR_WARPS = PR_THREADS / 32;
+constexpr int PR_CHUNK = 32;
+
+struct PRShared {
+    double models[PR_CHUNK][6];
+    int counts[PR_CHUNK];
+    int subsets[PR_CHUNK][5];
+    int niters, best, done_iters;
+    double best_model[6];
+};
+
+__global__ void __launch_bounds__(PR_THREADS)
+k_pnp_ransac(const float* __restrict__ points3d, const float* __restrict__ pts2d, const int32_t* __restrict__ n_corr,
+             int n_max, FSCamera cam_, double reproj_error, double confidence, int max_iters, int min_points,
+             double* __restrict__ model_out, uint8_t* __restrict__ mask_out, int32_t* __restrict__ inlier_idx,
+             int32_t* __restrict__ n_inliers, int32_t* __restrict__ iters_run, int32_t* __restrict__ status) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    PnPStage st;
+    st.carve(smem_raw, n_max);
+    PRShared& sh = *reinterpret_cast<PRShared*>(smem_raw + (PnPStage::bytes(n_max) + 15) / 16 * 16);
+    __shared__ int s_warp[33];
+
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(n_corr[p], n_max);
+    uint8_t* mask = mask_out + (size_t)p * n_max;
+    double* mo = model_out + 6 * (size_t)p;
+    const cvm::CamD cam = to_cam(cam_);
+
+    if (n < max(min_points, 5)) {  // stereo_slam.py:292 gate (6); below 5 OpenCV switches to P3P (not on the path)
+        for (int i = tid; i < n_max; i += PR_THREADS) mask[i] = 0;
+        if (tid < 6) mo[tid] = 0.0;
+        if (tid == 0) {
+            n_inliers[p] = 0;
+            if (iters_run) iters_run[p] = 0;
+            status[p] = FS_PAIR_TOO_FEW;
+        }
+        return;
+    }
+    st.load(points3d + 3 * (size_t)p * n_max, pts2d + 2 * (size_t)p * n_max, n);
+    const float thr2 = (float)(reproj_error * reproj_error);
+    cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
+    if (tid == 0) {
+        sh.niters = max(max_iters, 1);
+        sh.best = 0;
+        sh.done_iters = 0;
+    }
+    __syncthreads();
+
+    if (n == 5) {
+        // model_points == npoints: solvePnP(EPNP) on all points, every point an inlier, no refit
+        if (tid == 0) {
+            double obj[5][3];
+            float img[5][2];
+            for (int i = 0; i < 5; i++) {
+                obj[i][0] = st.X[i]; obj[i][1] = st.Y[i]; obj[i][2] = st.Z[i];
+                img[i][0] = st.u[i]; img[i][1] = st.v[i];
+            }
+            double m[6];
+            cvm::pnp_minimal_epnp5(cam, obj, img, m);
+            for (int i = 0; i < 6; i++) mo[i] = m[i];
+            n_inliers[p] = 5;
+            if (iters_run) iters_run[p] = 0;
+            status[p] = FS_PAIR_OK;
+        }
+        for (int i = tid; i < n_max; i += PR_THREADS) {
+            mask[i] = i < 5 ? 1 : 0;
+            if (inlier_idx && i < 5) inlier_idx[(size_t)p * n_max + i] = i;
+        }
+        return;
+    }
+
+    for (int base = 0;; base += PR_CHUNK) {
+        const int niters = sh.niters;
+        if (base >= niters) break;
+        const int round = min(PR_CHUNK, niters - base);
+        if (tid == 0) {
+            for (int s = 0; s < round; s++) {
+                int* idx = sh.subsets[s];
+                for (int i = 0; i < 5; i++) {
+                    int v;
+                    bool dup;
+                    do {
+                        v = rng.uniform(0, n);
+                        dup = false;
+                        for (int k = 0; k < i; k++) dup |= idx[k] == v;
+                    } while (dup);
+                    idx[i] = v;
+                }
+            }
+        }
+        __syncthreads();
+        if (tid < round) {
+            double obj[5][3];
+            float img[5][2];
+            for (int i = 0; i < 5; i++) {
+                const int k = sh.subsets[tid][i];
+                obj[i][0] = st.X[k]; obj[i][1] = st.Y[k]; obj[i][2] = st.Z[k];
+                img[i][0] = st.u[k]; img[i][1] = st.v[k];
+            }
+            double m[6];
+            cvm::pnp_minimal_epnp5(cam, obj, img, m);
+            for (int i = 0; i < 6; i++) sh.models[tid][i] = m[i];
+        }
+        __syncthreads();
+        for (int h = warp; h < round; h += PR_WARPS) {
+            double rv[3], t[3], R[9];
+            for (int i = 0; i < 3; i++) {
+                rv[i] = sh.models[h][i];
+                t[i] = sh.models[h][3 + i];
+            }
+            cvm::rodrigues_vec2mat(rv, R);
+            const int c = warp_count_reproj(R, t, cam, st, n, thr2, lane);
+            if (lane == 0) sh.counts[h] = c;
+        }
+        __syncthreads();
+        if (tid == 0) {
+            int nit = sh.niters, best = sh.best, done = sh.done_iters;
+            for (int s = 0; s < round; s++) {
+                const int it = base + s;
+                if (it >= nit) break;
+                const int c = sh.counts[s];
+                if (c > max(best, 4)) {
+                    best = c;
+                    for (int i = 0; i < 6; i++) sh.best_model[i] = sh.models[s][i];
+                    nit = cvm::ransac_update_num_iters(confidence, (double)(n - c) / n, 5, nit);
+                }
+                done = it + 1;
+            }
+            sh.niters = nit;
+            sh.best = best;
+            sh.done_iters = done;
+        }
+        __syncthreads();
+    }
+
+    const int best = sh.best;
+    if (best == 0) {
+        for (int i = tid; i < n_max; i += PR_THREADS) mask[i] = 0;
+        if (tid < 6) mo[tid] = 0.0;
+        if (tid == 0) {
+            n_inliers[p] = 0;
+            if (iters_run) iters_run[p] = sh.done_iters;
+            status[p] = FS_PAIR_NO_MODEL;
+        }
+        return;
+    }
+    double rv[3], t[3], R[9];
+    for (int i = 0; i < 3; i++) {
+        rv[i] = sh.best_model[i];
+        t[i] = sh.best_model[3 + i];
+    }
+    cvm::rodrigues_vec2mat(rv, R);
+    // mask of the winner (identical arithmetic to the scoring pass) + ascending inlier index list
+    int basei = 0;
+    for (int i0 = 0; i0 < n_max; i0 += PR_THREADS) {
+        const int i = i0 + tid;
+        bool in = false;
+        if (i < n) {
+            float pu, pv;
+            cvm::project_point_f32(R, t, cam, st.X[i], st.Y[i], st.Z[i], pu, pv);
+            in = cvm::reproj_err_f32(st.u[i], st.v[i], pu, pv) <= thr2;
+        }
+        if (i < n_max) mask[i] = in ? 1 : 0;
+        const unsigned bal = __ballot_sync(0xffffffffu, in);
+        __syncthreads();
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        if (warp == 0) {
+            int v = lane < PR_WARPS ? s_warp[lane] : 0, incl = v;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int nb = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += nb;
+            }
+            s_warp[lane] = incl - v;
+            if (lane == 31) s_warp[32] = incl;
+        }
+        __syncthreads();
+        if (in && inlier_idx)
+            inlier_idx[(size_t)p * n_max + basei + s_warp[warp] + __popc(bal & ((1u << lane) - 1))] = i;
+        basei += s_warp[32];
+    }
+    if (tid < 6) mo[tid] = sh.best_model[tid];
+    if (tid == 0) {
+        n_inliers[p] = best;
+        if (iters_run) iters_run[p] = sh.done_iters;
+        status[p] = FS_PAIR_OK;
+    }
+}
+
+
+// ------------------------------------------------------------------------------------------------ A7 refit
+// cv::solvePnPRansac ends with solvePnP(SOLVEPNP_ITERATIVE) on the consensus set: a Levenberg-Marquardt minimisation
+// of the distorted reprojection error over the 6 pose parameters.  OpenCV starts it from a DLT pose; here it starts
+// from the RANSAC winner and iterates to convergence on the same objective, so both land on the same minimum (the
+// target is 1e-4 rad / 1e-4 relative, not bit-exactness).  Rotation updates are multiplicative, R <- exp(d) R.
+// One CTA per pair; normal equations are reduced in a fixed order (deterministic).  Exactly 5 inliers: OpenCV's DLT
+// raises and solvePnPRansac falls back to the minimal-sample model — same here.
+constexpr int RF_THREADS = 256;
+constexpr int RF_WARPS = RF_THREADS / 32;
+constexpr int RF_NACC = 28;  // 21 (upper JtJ) + 6 (Jt e) + 1 (e^T e)
+constexpr int RF_MAX_ITERS = 40;
+
+struct RFState {
+    double R[9], t[3], H[21], g[6], err;
+    double Rc[9], tc[3], step2, lambda;
+    double part[RF_WARPS][RF_NACC];
+    double acc[RF_NACC];
+    int done;
+};
+
+__device__ __forceinline__ void refit_point(const double* R, const double* t, const cvm::CamD& cam, double Xw, double Yw,
+                                            double Zw, double u, double v, double* acc) {
+    const double qx = R[0] * Xw + R[1] * Yw + R[2] * Zw, qy = R[3] * Xw + R[4] * Yw + R[5] * Zw,
+                 qz = R[6] * Xw + R[7] * Yw + R[8] * Zw;
+    const double X = qx + t[0], Y = qy + t[1], Z = qz + t[2];
+    const double iz = Z != 0 ? 1. / Z : 1., x = X * iz, y = Y * iz;
+    const double k1 = cam.k[0], k2 = cam.k[1], p1 = cam.k[2], p2 = cam.k[3], k3 = cam.k[4];
+    const double r2 = x * x + y * y, cd = 1 + r2 * (k1 + r2 * (k2 + r2 * k3)), dcd = k1 + r2 * (2 * k2 + 3 * k3 * r2);
+    const double xd = x * cd + p1 * (2 * x * y) + p2 * (r2 + 2 * x * x);
+    const double yd = y * cd + p1 * (r2 + 2 * y * y) + p2 * (2 * x * y);
+    const double eu = cam.fx * xd + cam.cx - u, ev = cam.fy * yd + cam.cy - v;
+    const double xdx = cd + 2 * x * x * dcd + 2 * p1 * y + 6 * p2 * x, xdy = 2 * x * y * dcd + 2 * p1 * x + 2 * p2 * y;
+    const double ydx = 2 * x * y * dcd + 2 * p1 * x + 2 * p2 * y, ydy = cd + 2 * y * y * dcd + 6 * p1 * y + 2 * p2 * x;
+    // d(x, y)/dP
+    const double xP[3] = {iz, 0., -x * iz}, yP[3] = {0., iz, -y * iz};
+    double uP[3], vP[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        uP[k] = cam.fx * (xdx * xP[k] + xdy * yP[k]);
+        vP[k] = cam.fy * (ydx * xP[k] + ydy * yP[k]);
+    }
+    // dP/d(delta) = -[q]_x, dP/dt = I
+    double Ju[6], Jv[6];
+    Ju[0] = -uP[1] * qz + uP[2] * qy; Ju[1] = uP[0] * qz - uP[2] * qx; Ju[2] = -uP[0] * qy + uP[1] * qx;
+    Jv[0] = -vP[1] * qz + vP[2] * qy; Jv[1] = vP[0] * qz - vP[2] * qx; Jv[2] = -vP[0] * qy + vP[1] * qx;
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        Ju[3 + k] = uP[k];
+        Jv[3 + k] = vP[k];
+    }
+    int o = 0;
+#pragma unroll
+    for (int a = 0; a < 6; a++)
+#pragma unroll
+        for (int b = a; b < 6; b++) acc[o++] += Ju[a] * Ju[b] + Jv[a] * Jv[b];
+#pragma unroll
+    for (int a = 0; a < 6; a++) acc[21 + a] += Ju[a] * eu + Jv[a] * ev;
+    acc[27] += eu * eu + ev * ev;
+}
+
+// Cholesky solve of the damped 6x6 system; returns false if not positive definite
+__device__ bool solve6(const double* Hup, const double* g, double lambda, double* d) {
+    double A[6][6];
+    int o = 0;
+    for (int a = 0; a < 6; a++)
+        for (int b = a; b < 6; b++) {
+            A[a][b] = A[b][a] = Hup[o++];
+        }
+    for (int a = 0; a < 6; a++) A[a][a] += lambda * A[a][a] + 1e-300;
+    double L[6][6];
+    for (int i = 0; i < 6; i++)
+        for (int j = 0; j <= i; j++) {
+            double s = A[i][j];
+            for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
+            if (i == j) {
+                if (!(s > 0)) return false;
+                L[i][i] = sqrt(s);
+            } else {
+                L[i][j] = s / L[j][j];
+            }
+        }
+    double y[6];
+    for (int i = 0; i < 6; i++) {
+        double s = -g[i];
+        for (int k = 0; k < i; k++) s -= L[i][k] * y[k];
+        y[i] = s / L[i][i];
+    }
+    for (int i = 5; i >= 0; i--) {
+        double s = y[i];
+        for (int k = i + 1; k < 6; k++) s -= L[k][i] * d[k];
+        d[i] = s / L[i][i];
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(RF_THREADS)
+k_pnp_refine(const float* __restrict__ points3d, const float* __restrict__ pts2d, const int32_t* __restrict__ n_corr,
+             int n_max, FSCamera cam_, const double* __restrict__ model, const uint8_t* __restrict__ mask_in,
+             const int32_t* __restrict__ n_inliers, const int32_t* __restrict__ status, double* __restrict__ rvec,
+             double* __restrict__ tvec) {
+    __shared__ RFState S;
+    const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int n = min(n_corr[p], n_max);
+    const double* m = model + 6 * (size_t)p;
+    if (status[p] != FS_PAIR_OK || n_inliers[p] <= 5) {
+        if (tid < 3) {
+            rvec[3 * (size_t)p + tid] = m[tid];
+            tvec[3 * (size_t)p + tid] = m[3 + tid];
+        }
+        return;
+    }
+    const cvm::CamD cam = to_cam(cam_);
+    const float* p3 = points3d + 3 * (size_t)p * n_max;
+    const float2* p2 = reinterpret_cast<const float2*>(pts2d) + (size_t)p * n_max;
+    const uint8_t* mask = mask_in + (size_t)p * n_max;
+    if (tid == 0) {
+        double rv[3] = {m[0], m[1], m[2]};
+        cvm::rodrigues_vec2mat(rv, S.Rc);
+        for (int i = 0; i < 3; i++) S.tc[i] = m[3 + i];
+        S.lambda = 1e-3;
+        S.err = -1.0;  // no accepted state yet
+        S.done = 0;
+        S.step2 = 0;
+    }
+    __syncthreads();
+    for (int it = 0; it <= RF_MAX_ITERS; it++) {
+        // ---- evaluate the candidate (Rc, tc)
+        double acc[RF_NACC];
+#pragma unroll
+        for (int k = 0; k < RF_NACC; k++) acc[k] = 0;
+        double R[9], t[3];
+#pragma unroll
+        for (int k = 0; k < 9; k++) R[k] = S.Rc[k];
+#pragma unroll
+        for (int k = 0; k < 3; k++) t[k] = S.tc[k];
+        for (int i = tid; i < n; i += RF_THREADS) {
+            if (!mask[i]) continue;
+            const float2 uv = p2[i];
+            refit_point(R, t, cam, (double)p3[3 * i], (double)p3[3 * i + 1], (double)p3[3 * i + 2], (double)uv.x,
+                        (double)uv.y, acc);
+        }
+#pragma unroll
+        for (int k = 0; k < RF_NACC; k++) {
+            double v = acc[k];
+#pragma unroll
+            for (int o = 16; o >= 1; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+            if (lane == 0) S.part[warp][k] = v;
+        }
+        __syncthreads();
+        if (tid < RF_NACC) {
+            double v = 0;
+            for (int w = 0; w < RF_WARPS; w++) v += S.part[w][tid];
+            S.acc[tid] = v;
+        }
+        __syncthreads();
+        // ---- accept / reject, next step
+        if (tid == 0) {
+            const double errc = S.acc[27];
+            bool accepted = false;
+            if (S.err < 0 || errc < S.err) {
+                accepted = true;
+                const double prev = S.err;
+                for (int k = 0; k < 9; k++) S.R[k] = S.Rc[k];
+                for (int k = 0; k < 3; k++) S.t[k] = S.tc[k];
+                for (int k = 0; k < 21; k++) S.H[k] = S.acc[k];
+                for (int k = 0; k < 6; k++) S.g[k] = S.acc[21 + k];
+                S.err = errc;
+                if (prev >= 0) {
+                    S.lambda = fmax(S.lambda * 0.1, 1e-15);
+                    if (S.step2 < 1e-26 || (prev - errc) <= 1e-15 * prev) S.done = 1;
+                }
+            } else {
+                S.lambda *= 10.;
+                if (S.lambda > 1e12) S.done = 1;
+            }
+            (void)accepted;
+            if (!S.done && it < RF_MAX_ITERS) {
+                double d[6];
+                bool ok = solve6(S.H, S.g, S.lambda, d);
+                while (!ok && S.lambda < 1e12) {
+                    S.lambda = fmax(S.lambda * 10., 1e-6);
+                    ok = solve6(S.H, S.g, S.lambda, d);
+                }
+                if (!ok) {
+                    S.done = 1;
+                } else {
+                    double dR[9];
+                    cvm::rodrigues_vec2mat(d, dR);
+                    cvm::matmul33(dR, S.R, S.Rc);
+                    for (int k = 0; k < 3; k++) S.tc[k] = S.t[k] + d[3 + k];
+                    S.step2 = d[0] * d[0] + d[1] * d[1] + d[2] * d[2] + d[3] * d[3] + d[4] * d[4] + d[5] * d[5];
+                }
+            }
+        }
+        __syncthreads();
+        if (S.done) break;
+    }
+    if (tid == 0) {
+        double rv[3];
+        cvm::rodrigues_mat2vec(S.R, rv);
+        for (int k = 0; k < 3; k++) {
+            rvec[3 * (size_t)p + k] = rv[k];
+            tvec[3 * (size_t)p + k] = S.t[k];
+        }
+    }
+}
+
 }  // namespace
 
 extern "C" int fs_score_pnp(const float* points3d, const float* pts2d, const int32_t* n_corr, int n_pairs, int n_max,
@@ -99,11 +506,38 @@ extern "C" int fs_score_pnp(const float* points3d, const float* pts2d, const int
     return FS_OK;
 }
 
-extern "C" size_t fs_solve_pnp_workspace_bytes(int, int, int) { return 256; }
 
-extern "C" int fs_solve_pnp_ransac(const float*, const float*, const int32_t*, int, int, const FSCamera*, double,
-                                   double, int, int, double*, double*, uint8_t*, int32_t*, int32_t*, int32_t*,
-                                   int32_t*, void*, size_t, fs_stream_t) {
-    fs::set_error("fs_solve_pnp_ransac: EPnP minimal solver not built yet");
-    return FS_ERR_UNSUPPORTED;
+extern "C" size_t fs_solve_pnp_workspace_bytes(int n_pairs, int, int) {
+    return fs::align_up((size_t)(n_pairs > 0 ? n_pairs : 1) * 6 * sizeof(double), 256) + 256;
+}
+
+extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, const int32_t* n_corr, int n_pairs,
+                                   int n_max, const FSCamera* cam, double reproj_error, double confidence,
+                                   int max_iters, int min_points, double* rvec, double* tvec, uint8_t* mask,
+                                   int32_t* inlier_idx, int32_t* n_inliers, int32_t* iters_run, int32_t* status,
+                                   void* workspace, size_t workspace_bytes, fs_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    FS_REQUIRE(n_pairs >= 0 && n_max >= 0, "negative size");
+    if (n_pairs == 0) return FS_OK;
+    FS_REQUIRE(n_max >= 1, "n_max must be positive");
+    FS_REQUIRE(points3d && pts2d && n_corr && cam && rvec && tvec && mask && n_inliers && status, "null pointer");
+    FS_REQUIRE(confidence > 0 && confidence < 1, "confidence must be in (0, 1)");
+    if (!workspace || workspace_bytes < fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters)) {
+        fs::set_error("fs_solve_pnp_ransac: workspace %zu < %zu", workspace_bytes,
+                      fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters));
+        return FS_ERR_WORKSPACE;
+    }
+    fs::Carver ws(workspace);
+    double* model = ws.take<double>((size_t)n_pairs * 6);
+    const size_t smem = fs::align_up(PnPStage::bytes(n_max), 16) + sizeof(PRShared) + 16;
+    FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~7000)");
+    FS_CUDA(cudaFuncSetAttribute(k_pnp_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_pnp_ransac<<<n_pairs, PR_THREADS, smem, stream>>>(points3d, pts2d, n_corr, n_max, *cam, reproj_error, confidence,
+                                                       max_iters, min_points, model, mask, inlier_idx, n_inliers,
+                                                       iters_run, status);
+    FS_LAUNCH_CHECK("k_pnp_ransac");
+    k_pnp_refine<<<n_pairs, RF_THREADS, 0, stream>>>(points3d, pts2d, n_corr, n_max, *cam, model, mask, n_inliers,
+                                                    status, rvec, tvec);
+    FS_LAUNCH_CHECK("k_pnp_refine");
+    return FS_OK;
 }

@@ -3,6 +3,7 @@
 // kernels execute against cv2 without a GPU.  Never loaded by the product path.
 #include "../../forest_slam_b200/csrc/fivepoint.cuh"
 #include "../../forest_slam_b200/csrc/posemath.cuh"
+#include "../../forest_slam_b200/csrc/epnp.cuh"
 #include <vector>
 
 extern "C" {
@@ -119,5 +120,91 @@ int hh_recover_pose(const double* E, const float* p0, const float* p1, int n, do
     for (int i = 0; i < 3; i++) t_out[i] = (best & 2) ? tm[i] : tp[i];
     for (int i = 0; i < n; i++) mask[i] = ((bits[i] >> best) & 1) ? 255 : 0;
     return cnt[best];
+}
+
+static cvm::CamD hh_cam(const double* cam9) {
+    cvm::CamD c;
+    c.fx = cam9[0]; c.fy = cam9[1]; c.cx = cam9[2]; c.cy = cam9[3];
+    for (int i = 0; i < 5; i++) c.k[i] = cam9[4 + i];
+    return c;
+}
+// cam9 = fx fy cx cy k1 k2 p1 p2 k3
+void hh_undistort(const float* uv, int n, const double* cam9, float* out) {
+    const cvm::CamD c = hh_cam(cam9);
+    for (int i = 0; i < n; i++) cvm::undistort_point_f32(uv[2 * i], uv[2 * i + 1], c, out[2 * i], out[2 * i + 1]);
+}
+void hh_epnp5(const float* obj, const float* img, const double* cam9, double* model) {
+    const cvm::CamD c = hh_cam(cam9);
+    double o[5][3];
+    float im[5][2];
+    for (int i = 0; i < 5; i++) {
+        for (int j = 0; j < 3; j++) o[i][j] = (double)obj[3 * i + j];
+        im[i][0] = img[2 * i];
+        im[i][1] = img[2 * i + 1];
+    }
+    cvm::pnp_minimal_epnp5(c, o, im, model);
+}
+void hh_svd_solve64(const double* A, const double* b, double* x) { cvm::svd_solve<6, 4>(A, b, x); }
+void hh_svd_invert3(const double* A, double* inv) { cvm::svd_invert3(A, inv); }
+void hh_svd12(const double* A, double* w, double* ut) {
+    double At[144], vt[144];
+    for (int i = 0; i < 12; i++) for (int j = 0; j < 12; j++) At[j * 12 + i] = A[i * 12 + j];
+    cvm::jacobi_svd<12, 12, 12>(At, 12, w, vt);
+    for (int i = 0; i < 144; i++) ut[i] = At[i];
+}
+void hh_rodrigues_mat2vec(const double* R, double* r) { cvm::rodrigues_mat2vec(R, r); }
+
+// serial solvePnPRansac (RANSAC stage only: EPnP minimal sets, float32 reprojection test, adaptive cap) from the SAME
+// header code k_pnp_ransac runs.  model_out = rvec|tvec of the best minimal-sample model; returns the inlier count.
+int hh_pnp_ransac(const float* p3, const float* p2, int n, const double* cam9, double reproj, double conf, int max_iters,
+                  double* model_out, unsigned char* mask, int* iters) {
+    const cvm::CamD cam = hh_cam(cam9);
+    const float thr2 = (float)(reproj * reproj);
+    cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
+    int niters = max_iters > 1 ? max_iters : 1, best = 0, it = 0;
+    double bm[6] = {0};
+    for (it = 0; it < niters; it++) {
+        int idx[5];
+        for (int i = 0; i < 5; i++) {
+            int v;
+            bool dup;
+            do {
+                v = rng.uniform(0, n);
+                dup = false;
+                for (int k = 0; k < i; k++) dup |= idx[k] == v;
+            } while (dup);
+            idx[i] = v;
+        }
+        double obj[5][3], m[6], R[9];
+        float img[5][2];
+        for (int i = 0; i < 5; i++) {
+            for (int j = 0; j < 3; j++) obj[i][j] = (double)p3[3 * idx[i] + j];
+            img[i][0] = p2[2 * idx[i]];
+            img[i][1] = p2[2 * idx[i] + 1];
+        }
+        cvm::pnp_minimal_epnp5(cam, obj, img, m);
+        cvm::rodrigues_vec2mat(m, R);
+        int c = 0;
+        for (int i = 0; i < n; i++) {
+            float pu, pv;
+            cvm::project_point_f32(R, m + 3, cam, (double)p3[3 * i], (double)p3[3 * i + 1], (double)p3[3 * i + 2], pu, pv);
+            c += cvm::reproj_err_f32(p2[2 * i], p2[2 * i + 1], pu, pv) <= thr2;
+        }
+        if (c > (best > 4 ? best : 4)) {
+            best = c;
+            for (int i = 0; i < 6; i++) bm[i] = m[i];
+            niters = cvm::ransac_update_num_iters(conf, (double)(n - c) / n, 5, niters);
+        }
+    }
+    *iters = it;
+    double R[9];
+    cvm::rodrigues_vec2mat(bm, R);
+    for (int i = 0; i < 6; i++) model_out[i] = bm[i];
+    for (int i = 0; i < n; i++) {
+        float pu, pv;
+        cvm::project_point_f32(R, bm + 3, cam, (double)p3[3 * i], (double)p3[3 * i + 1], (double)p3[3 * i + 2], pu, pv);
+        mask[i] = best ? (cvm::reproj_err_f32(p2[2 * i], p2[2 * i + 1], pu, pv) <= thr2) : 0;
+    }
+    return best;
 }
 }

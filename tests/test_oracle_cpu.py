@@ -175,3 +175,94 @@ def test_degenerate_inputs_of_cv2():
     assert E is None and mask is None
     assert cv2.BFMatcher(cv2.NORM_HAMMING, crossCheck=True).match(np.zeros((0, 32), np.uint8),
                                                                    np.zeros((3, 32), np.uint8)) == ()
+
+
+# ------------------------------------------------------------------------------------------------ A7 (PnP) pins
+CAM9 = np.array([lit.K0[0, 0], lit.K0[1, 1], lit.K0[0, 2], lit.K0[1, 2], *lit.DIST_L])
+
+
+def test_jacobi_svd_bit_exact_vs_cv2():
+    """The Jacobi SVD restatement (csrc/cvmath.cuh) is BIT-exact against cv2.SVDecomp, including the rank-10 12x12
+    case whose null-space basis is decided by rounding noise (this is what EPnP on 5 points depends on)."""
+    hh = util.host_harness()
+    rng = np.random.default_rng(0)
+    for rows in (30, 10):
+        for _ in range(40):
+            M = rng.normal(size=(rows, 12))
+            S = M.T @ M
+            w, ut = np.zeros(12), np.zeros(144)
+            hh.hh_svd12(util.vp(S), util.vp(w), util.vp(ut))
+            w2, u2, _ = cv2.SVDecomp(S)
+            assert np.array_equal(w, w2.ravel()) and np.array_equal(ut.reshape(12, 12), u2.T)
+    for n, fn in ((3, hh.hh_svd33), (4, hh.hh_svd44)):
+        for _ in range(40):
+            A = rng.normal(size=(n, n))
+            w, u, vt = np.zeros(n), np.zeros(n * n), np.zeros(n * n)
+            fn(util.vp(A), util.vp(w), util.vp(u), util.vp(vt))
+            w2, u2, vt2 = cv2.SVDecomp(A)
+            assert np.array_equal(w, w2.ravel()) and np.array_equal(u.reshape(n, n), u2)
+            assert np.array_equal(vt.reshape(n, n), vt2)
+
+
+def test_epnp_building_blocks_bit_exact():
+    hh = util.host_harness()
+    rng = np.random.default_rng(1)
+    for _ in range(20):
+        A = rng.normal(size=(3, 3))
+        inv = np.zeros(9)
+        hh.hh_svd_invert3(util.vp(A), util.vp(inv))
+        assert np.array_equal(inv.reshape(3, 3), cv2.invert(A, flags=cv2.DECOMP_SVD)[1])
+        A = rng.normal(size=(6, 4))
+        b = rng.normal(size=(6, 1))
+        x = np.zeros(4)
+        hh.hh_svd_solve64(util.vp(A), util.vp(b), util.vp(x))
+        assert np.array_equal(x, cv2.solve(A, b, flags=cv2.DECOMP_SVD)[1].ravel())
+        R = cv2.Rodrigues(rng.normal(0, 0.4, 3))[0]
+        r = np.zeros(3)
+        hh.hh_rodrigues_mat2vec(util.vp(np.ascontiguousarray(R)), util.vp(r))
+        assert np.abs(r - cv2.Rodrigues(R)[0].ravel()).max() < 1e-15
+    uv = rng.uniform(0, 900, (500, 2)).astype(np.float32)
+    out = np.zeros((500, 2), np.float32)
+    hh.hh_undistort(util.vp(uv), 500, util.vp(CAM9), util.vp(out))
+    assert np.array_equal(out, cv2.undistortPoints(uv.reshape(-1, 1, 2), lit.K0, lit.DIST_L).reshape(-1, 2))
+
+
+def test_epnp5_bit_exact_vs_cv2():
+    """The minimal solver of solvePnPRansac: cv2.solvePnP(flags=SOLVEPNP_EPNP) on 5 points."""
+    hh = util.host_harness()
+    for seed in range(150):
+        P3, p2, _, _ = util.pnp_scene(5, 9000 + seed, outliers=0.0)
+        _, rv, tv = cv2.solvePnP(P3, p2, lit.K0, lit.DIST_L, flags=cv2.SOLVEPNP_EPNP)
+        m = np.zeros(6)
+        hh.hh_epnp5(util.vp(P3), util.vp(p2), util.vp(CAM9), util.vp(m))
+        assert np.abs(m[:3] - rv.ravel()).max() < 1e-12 and np.abs(m[3:] - tv.ravel()).max() < 1e-12, seed
+
+
+def _hh_pnp_ransac(P3, p2):
+    hh = util.host_harness()
+    hh.hh_pnp_ransac.restype = C.c_int
+    hh.hh_pnp_ransac.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_double, C.c_double, C.c_int,
+                                 C.c_void_p, C.c_void_p, C.c_void_p]
+    n = P3.shape[0]
+    m = np.zeros(6)
+    mask = np.zeros(n, np.uint8)
+    it = C.c_int(0)
+    c = hh.hh_pnp_ransac(util.vp(P3), util.vp(p2), n, util.vp(CAM9), 1.0, 0.99, 1000, util.vp(m), util.vp(mask),
+                         C.byref(it))
+    return c, m, mask, it.value
+
+
+@pytest.mark.parametrize("i", [0, 1, 2])
+def test_pnp_ransac_host_code_vs_golden(i):
+    c, _, mask, _ = _hh_pnp_ransac(G[f"pnp{i}_P3"], G[f"pnp{i}_p2"])
+    assert bool(G[f"pnp{i}_ok"])
+    assert np.array_equal(np.nonzero(mask)[0], G[f"pnp{i}_inliers"].ravel())
+
+
+@pytest.mark.parametrize("seed", range(9))
+def test_pnp_ransac_host_code_vs_cv2_live(seed):
+    n = [40, 400, 1500][seed % 3]
+    P3, p2, _, _ = util.pnp_scene(n, 4100 + seed, outliers=[0.1, 0.3, 0.5][(seed // 3) % 3])
+    ok, _, _, inl = lit.solve_pnp_ransac(P3, p2)
+    c, _, mask, _ = _hh_pnp_ransac(P3, p2)
+    assert ok and np.array_equal(np.nonzero(mask)[0], inl.ravel())

@@ -157,3 +157,131 @@ def test_pose_algebra(fsb):
                                      torch.from_numpy(T[:2]).cuda()).cpu().numpy()
     ref = (np.concatenate([pts[1, :60], np.ones((60, 1), np.float32)], 1) @ T[1].T)[:, :3]  # stereo_slam.py:309-311
     assert np.allclose(out[1, :60], ref, rtol=1e-6, atol=1e-5)
+
+
+# ------------------------------------------------------------------------------------------------ A7 (PnP)
+def _check_pnp(fsb, P3, p2):
+    ok_cv, rvec_cv, tvec_cv, inl_cv = lit.solve_pnp_ransac(P3, p2)
+    ok, rvec, tvec, inl = fsb.solvePnPRansac(P3, p2, lit.K0, lit.DIST_L, reprojectionError=1.0, confidence=0.99,
+                                             iterationsCount=1000, flags=fsb.SOLVEPNP_ITERATIVE)
+    assert ok == ok_cv
+    if not ok:
+        return
+    assert np.array_equal(inl, inl_cv)
+    R, R_cv = fsb.Rodrigues(rvec)[0], fsb.Rodrigues(rvec_cv)[0]
+    assert lit.angle_error_mat(R, R_cv) < ROT_TOL
+    assert np.linalg.norm(tvec - tvec_cv) < 1e-4 * max(1.0, np.linalg.norm(tvec_cv))
+
+
+@pytest.mark.parametrize("i", [0, 1, 2])
+def test_pnp_golden(fsb, i):
+    ok, rvec, tvec, inl = fsb.solvePnPRansac(G[f"pnp{i}_P3"], G[f"pnp{i}_p2"], lit.K0, lit.DIST_L,
+                                             reprojectionError=1.0, confidence=0.99, iterationsCount=1000,
+                                             flags=fsb.SOLVEPNP_ITERATIVE)
+    assert ok == bool(G[f"pnp{i}_ok"]) and np.array_equal(inl, G[f"pnp{i}_inliers"])
+    assert lit.angle_error_mat(fsb.Rodrigues(rvec)[0], fsb.Rodrigues(G[f"pnp{i}_rvec"])[0]) < ROT_TOL
+    assert np.linalg.norm(tvec - G[f"pnp{i}_tvec"]) < 1e-4
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_pnp_vs_cv2(fsb, seed):
+    n = [12, 300, 1200, 2000][seed % 4]
+    P3, p2, _, _ = util.pnp_scene(n, 8000 + seed, outliers=[0.1, 0.3, 0.5, 0.2][(seed // 4) % 4])
+    _check_pnp(fsb, P3, p2)
+
+
+def test_pnp_five_points_and_gate(fsb):
+    import torch
+    P3, p2, _, _ = util.pnp_scene(5, 77, outliers=0.0)
+    _check_pnp(fsb, P3, p2)  # model_points == npoints: EPnP on all points, no RANSAC, no refit
+    # the >= 6 gate of stereo_slam.py:292 in the batched operator; ragged batch equals pair-by-pair cv2
+    sizes = [700, 5, 0, 64, 700]
+    n_max = 700
+    P = len(sizes)
+    b3 = np.zeros((P, n_max, 3), np.float32)
+    b2 = np.zeros((P, n_max, 2), np.float32)
+    for p, n in enumerate(sizes):
+        a, b, _, _ = util.pnp_scene(max(n, 1), 600 + p, outliers=0.3 if n > 10 else 0.0)
+        b3[p, :n], b2[p, :n] = a[:n], b[:n]
+    r = fsb.solve_pnp_ransac_batch(torch.from_numpy(b3).cuda(), torch.from_numpy(b2).cuda(),
+                                   torch.tensor(sizes, dtype=torch.int32).cuda(), min_points=6)
+    assert r["status"].cpu().numpy().tolist() == [0, 1, 1, 0, 0]
+    for p, n in enumerate(sizes):
+        if n >= 6:
+            ok, rv, tv, inl = lit.solve_pnp_ransac(b3[p, :n], b2[p, :n])
+            k = int(r["n_inliers"][p])
+            assert np.array_equal(r["inlier_idx"][p, :k].cpu().numpy(), inl.ravel()), p
+            assert np.array_equal(np.nonzero(r["mask"][p].cpu().numpy())[0], inl.ravel())
+            assert lit.angle_error_mat(fsb.Rodrigues(r["rvec"][p].cpu().numpy())[0], fsb.Rodrigues(rv)[0]) < ROT_TOL
+            assert np.linalg.norm(r["tvec"][p].cpu().numpy() - tv.ravel()) < 1e-4
+        else:
+            assert int(r["n_inliers"][p]) == 0 and not r["mask"][p].any()
+
+
+def test_score_pnp_sweep(fsb):
+    """Config-4 scoring sweep: counts of arbitrary (rvec|tvec) hypotheses equal cv2.projectPoints + float32 test."""
+    import torch
+    cv2 = pytest.importorskip("cv2")
+    P3, p2, _, _ = util.pnp_scene(900, 91, outliers=0.3)
+    ok, rv, tv, _ = lit.solve_pnp_ransac(P3, p2)
+    rng = np.random.default_rng(4)
+    models = np.concatenate([rv.ravel(), tv.ravel()])[None] + rng.normal(0, 2e-3, (256, 6))
+    models[0] = np.concatenate([rv.ravel(), tv.ravel()])
+    cnt = fsb.score_pnp_batch(torch.from_numpy(P3[None]).cuda(), torch.from_numpy(p2[None]).cuda(),
+                              torch.tensor([900], dtype=torch.int32).cuda(),
+                              torch.from_numpy(models[None]).cuda()).cpu().numpy()[0]
+    ref = []
+    for m in models:
+        proj = cv2.projectPoints(P3, m[:3], m[3:], lit.K0, lit.DIST_L)[0].reshape(-1, 2).astype(np.float32)
+        d = p2 - proj
+        ref.append(int(((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) <= np.float32(1.0)).sum()))
+    assert np.array_equal(cnt, np.array(ref))
+
+
+def test_stereo_sequence_driver(fsb):
+    """stereo_slam.py:210-306 through the batched driver equals the literal per-pair reference calls."""
+    import torch
+    from forest_slam_b200 import sequence as seq, synth
+    world = synth.make_world(n_trunks=80, n_ground=2500, n_canopy=2500)
+    frames = synth.make_sequence(5, 800, world=world)
+    kp, dbin, df, disp, counts = synth.stack_frames(frames)
+    bank = seq.FrameBank.from_numpy(kp, counts, desc_bin=dbin, disparity=disp)
+    res = seq.stereo_pairs(bank, [0, 1, 2, 3], [1, 2, 3, 4])
+    for p in range(4):
+        a, b = frames[p], frames[p + 1]
+        ref = lit.stereo_frame_pair(a.kpts, a.desc_bin, a.disparity, b.kpts, b.desc_bin)
+        k = int(res["n_points"][p])
+        assert k == ref["points3D"].shape[0]
+        assert np.allclose(res["points3d"][p, :k].cpu().numpy(), ref["points3D"], rtol=1e-3)
+        assert ref["ok"]
+        ni = int(res["n_inliers"][p])
+        assert np.array_equal(res["inlier_idx"][p, :ni].cpu().numpy(), ref["inliers"].ravel())
+        assert lit.angle_error_mat(res["R"][p].cpu().numpy(), ref["R"]) < ROT_TOL
+        assert np.linalg.norm(res["t"][p].cpu().numpy() - ref["tvec"].ravel()) < 1e-4
+
+
+def test_mono_sequence_driver(fsb):
+    import torch
+    from forest_slam_b200 import sequence as seq, synth
+    world = synth.make_world(n_trunks=80, n_ground=2500, n_canopy=2500)
+    frames = synth.make_sequence(4, 768, world=world)
+    kp, dbin, df, disp, counts = synth.stack_frames(frames)
+    bank = seq.FrameBank.from_numpy(kp, counts, desc_f32=df)
+    res = seq.mono_pairs(bank, [0, 1, 2], [1, 2, 3], scale=0.0625, threshold=float(np.log(0.2)))
+    for p in range(3):
+        a, b = frames[p], frames[p + 1]
+        ref = lit.mono_frame_pair(a.kpts, a.desc_f32, b.kpts, b.desc_f32)
+        k = int(res["n_matches"][p])
+        assert k == ref["mkpts0"].shape[0] and np.array_equal(res["mkpts0"][p, :k].cpu().numpy(), ref["mkpts0"])
+        assert np.array_equal(res["inlier_mask"][p, :k].cpu().numpy(), ref["mask"].ravel())
+        assert np.array_equal(res["pose_mask"][p, :k].cpu().numpy(), ref["pose_mask"].ravel())
+        assert lit.angle_error_mat(res["R"][p].cpu().numpy(), ref["R"]) < ROT_TOL
+        assert lit.angle_error_vec(res["t"][p].cpu().numpy(), ref["t"]) < DIR_TOL
+    rec = seq.pack_records(res)
+    T = seq.trajectory(seq.gather_records(rec, 3)).cpu().numpy()
+    acc = np.eye(4)
+    for p in range(3):
+        Ti = np.eye(4)
+        Ti[:3, :3], Ti[:3, 3] = res["R"][p].cpu().numpy(), res["t"][p].cpu().numpy()
+        acc = acc @ Ti
+    assert np.abs(T[2] - acc).max() < 1e-9
