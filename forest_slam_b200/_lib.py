@@ -35,6 +35,7 @@ SIGNATURES = {
                                    ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_prepare": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr]),
     "fs_float_match_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "fs_float_match_tc_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fs_float_match": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,
                                  C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_match_fp32": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,

@@ -33,7 +33,7 @@ SOLVEPNP_ITERATIVE = 0
 
 # the tcgen05 float matcher (csrc/float_tc.cu) is selected by default once it is built; the exact-fp32 CUDA-core
 # kernel serves descriptor counts that are not a multiple of 128 and `exact_fp32=True`
-TENSOR_CORE_MATCHER = False
+TENSOR_CORE_MATCHER = True
 
 DMatch = collections.namedtuple("DMatch", ["queryIdx", "trainIdx", "distance"])
 
@@ -151,7 +151,7 @@ def hamming_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b
 
 # ------------------------------------------------------------------------------------------- A1
 def float_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
-    """[F, 256, n_max] fp32 channel-major (SuperPoint layout) → [F, n_max, 512] split-bf16 operand bank."""
+    """[F, 256, n_max] fp32 channel-major (SuperPoint layout) → [F, n_max, 512] split-fp16 (hi | lo) operand bank."""
     lib = _lib.load()
     desc = _chk(desc, torch.float32, "desc")
     if desc.dim() != 3 or desc.shape[1] != 256:
@@ -159,7 +159,7 @@ def float_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
     dev = desc.device
     F, n_max = int(desc.shape[0]), int(desc.shape[2])
     counts = _chk(counts.to(dev), torch.int32, "counts")
-    ops = torch.empty((F, n_max, 512), dtype=torch.bfloat16, device=dev)
+    ops = torch.empty((F, n_max, 512), dtype=torch.float16, device=dev)
     _lib.check(lib.fs_float_prepare(_p(desc), F, n_max, _p(counts), _p(ops), _stream()), "fs_float_prepare")
     return ops
 
@@ -169,7 +169,7 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
                       operands: Optional[torch.Tensor] = None, exact_fp32: bool = False):
     """Batched float-descriptor mutual-NN (+threshold, +ratio): superglue.py:259-260, :268-278.
 
-    desc [F, 256, n_max] fp32.  The tensor-core path (default when n_max % 128 == 0) reads the split-bf16
+    desc [F, 256, n_max] fp32.  The tensor-core path (default when n_max % 128 == 0) reads the split-fp16
     operand bank (``operands`` or prepared on the fly); ``exact_fp32`` selects the CUDA-core fp32 kernel."""
     lib = _lib.load()
     if desc is not None:
@@ -191,9 +191,9 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
     nm = torch.empty((P,), dtype=torch.int32, device=dev)
     thr = -math.inf if threshold is None else float(threshold)
     rat = float(ratio) if ratio else 0.0
-    nbytes = lib.fs_float_match_workspace_bytes(P, n_max)
-    ws = _workspace(nbytes, dev)
     use_tc = TENSOR_CORE_MATCHER and (not exact_fp32) and n_max % 128 == 0
+    nbytes = lib.fs_float_match_tc_workspace_bytes(P, n_max) if use_tc else lib.fs_float_match_workspace_bytes(P, n_max)
+    ws = _workspace(nbytes, dev)
     if use_tc:
         if operands is None:
             operands = float_prepare(desc, counts)

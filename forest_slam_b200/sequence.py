@@ -26,7 +26,7 @@ class FrameBank:
     desc_f32: Optional[torch.Tensor] = None  # [F, 256, n_max] f32 (SuperPoint layout)
     desc_bin: Optional[torch.Tensor] = None  # [F, n_max, 32] u8 (ORB layout)
     disparity: Optional[torch.Tensor] = None  # [F, n_max] f32 per-keypoint disparity (uL - uR)
-    operands: Optional[torch.Tensor] = None  # [F, n_max, 512] bf16 split operands of the tensor-core matcher
+    operands: Optional[torch.Tensor] = None  # [F, n_max, 512] fp16 hi|lo split operands of the tensor-core matcher
 
     @staticmethod
     def from_numpy(kpts, counts, desc_f32=None, desc_bin=None, disparity=None, device="cuda") -> "FrameBank":

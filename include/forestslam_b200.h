@@ -91,12 +91,12 @@ int fs_hamming_match(const uint8_t* desc, int n_frames, int n_max, const int32_t
  *     plus the Lowe ratio of the north star on L2 distance d = sqrt(max(0, 2 - 2 s)) of unit vectors.
  *
  * Two-step: fs_float_prepare() turns a frame bank of channel-major fp32 descriptors (SuperPoint layout
- * [256, n], superpoint.py:90-91) into the K-major split-bf16 operand bank the tensor-core kernel reads
+ * [256, n], superpoint.py:90-91) into the K-major split-fp16 operand bank the tensor-core kernel reads
  * (once per FRAME, not per pair); fs_float_match() then runs the tcgen05 contraction with the fused
  * row top-2 epilogue for both directions and the mutual / threshold / ratio finalisation.
  *
  * desc_f32   [n_frames, 256, n_max] f32   channel-major
- * operands   [n_frames, n_max, 512] bf16  (hi | lo split; rows >= count are zero)
+ * operands   [n_frames, n_max, 512] fp16  (hi | lo split, x = hi + lo to 2^-25; rows >= count are zero)
  * scale      multiplies the raw dot product (superglue.py:260 uses 1/sqrt(256) = 0.0625); 1.0 = cosine
  * threshold  keep only if scaled best score > threshold (use -inf to disable)
  * ratio      <=0: off; else keep only if d_best < ratio * d_second (float32, strict), d from raw cosine
@@ -105,9 +105,10 @@ int fs_hamming_match(const uint8_t* desc, int n_frames, int n_max, const int32_t
  * ---------------------------------------------------------------------------------------------- */
 #define FS_FLOAT_DIM 256
 int fs_float_prepare(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
-                     void* operands_bf16, fs_stream_t stream);
-size_t fs_float_match_workspace_bytes(int n_pairs, int n_max);
-int fs_float_match(const void* operands_bf16, int n_frames, int n_max, const int32_t* counts,
+                     void* operands_fp16, fs_stream_t stream);
+size_t fs_float_match_workspace_bytes(int n_pairs, int n_max);    /* fs_float_match_fp32 */
+size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max); /* fs_float_match */
+int fs_float_match(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
                    const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
                    float scale, float threshold, float ratio,
                    int32_t* matches0, float* score0, float* second0, int32_t* matches1,

@@ -89,7 +89,7 @@ def test_hamming_batch_ragged(fsb):
 @pytest.mark.parametrize("n0,n1,seed,thr,ratio", [(1024, 1024, 1, None, None), (1000, 777, 2, 0.2, None),
                                                   (640, 1100, 3, None, 0.8), (1, 5, 4, None, None),
                                                   (4096, 4096, 5, 0.5, 0.9)])
-@pytest.mark.parametrize("exact", [True])
+@pytest.mark.parametrize("exact", [True, False])
 def test_float_mutual_nn(fsb, n0, n1, seed, thr, ratio, exact):
     d0, d1 = util.float_descriptors(n0, n1, seed)
     ref = lit.float_mutual_nn(d0, d1, threshold=thr, ratio=ratio)
@@ -98,7 +98,8 @@ def test_float_mutual_nn(fsb, n0, n1, seed, thr, ratio, exact):
     assert keep.mean() > 0.95
     assert np.array_equal(got["matches0"][keep], ref["matches0"][keep])
     ok = ref["matches0"] >= 0
-    assert np.allclose(got["matching_scores0"][ok & keep], ref["score0"][ok & keep], atol=2e-6)
+    # exact-fp32 kernel: fp32 FMA chain; tensor-core kernel: split-fp16 products with the MMA's fp32 accumulation
+    assert np.allclose(got["matching_scores0"][ok & keep], ref["score0"][ok & keep], atol=2e-6 if exact else 6e-6)
     # matches1 is the inverse permutation of matches0 (superglue.py:271-278)
     m0, m1 = got["matches0"], got["matches1"]
     q = np.nonzero(m0 >= 0)[0]
