@@ -220,8 +220,8 @@ def gather_matches_batch(kpts: torch.Tensor, counts: torch.Tensor, pair_a, pair_
     a, b = _pairs(pair_a, pair_b, dev)
     P = int(a.numel())
     matches0 = _chk(matches0, torch.int32, "matches0")
-    mk0 = torch.zeros((P, n_max, 2), dtype=torch.float32, device=dev)
-    mk1 = torch.zeros_like(mk0)
+    mk0 = torch.empty((P, n_max, 2), dtype=torch.float32, device=dev)  # rows >= n_corr[p] are never read
+    mk1 = torch.empty_like(mk0)
     nc = torch.empty((P,), dtype=torch.int32, device=dev)
     src = torch.empty((P, n_max), dtype=torch.int32, device=dev)
     _lib.check(lib.fs_gather_matches(_p(kpts), F, n_max, _p(counts), _p(a), _p(b), P, _p(matches0), _p(mk0),
@@ -268,8 +268,8 @@ def backproject_filter_batch(mkpts0, mkpts1, disparity, n_corr, *, camera: Fores
     n_corr = _chk(n_corr, torch.int32, "n_corr")
     dev = mkpts0.device
     P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
-    p3 = torch.zeros((P, n_max, 3), dtype=torch.float32, device=dev)
-    p2 = torch.zeros((P, n_max, 2), dtype=torch.float32, device=dev)
+    p3 = torch.empty((P, n_max, 3), dtype=torch.float32, device=dev)  # rows >= n_out[p] are never read
+    p2 = torch.empty((P, n_max, 2), dtype=torch.float32, device=dev)
     no = torch.empty((P,), dtype=torch.int32, device=dev)
     cam = camera.as_struct()
     B = camera.baseline if baseline is None else float(baseline)
@@ -289,11 +289,11 @@ def find_essential_batch(mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[floa
     n_corr = _chk(n_corr, torch.int32, "n_corr")
     dev = mkpts0.device
     P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
-    E = torch.zeros((P, 3, 3), dtype=torch.float64, device=dev)
-    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
-    ninl = torch.zeros((P,), dtype=torch.int32, device=dev)
-    iters = torch.zeros((P,), dtype=torch.int32, device=dev)
-    status = torch.zeros((P,), dtype=torch.int32, device=dev)
+    E = torch.empty((P, 3, 3), dtype=torch.float64, device=dev)  # the kernel writes every output of every pair
+    mask = torch.empty((P, n_max), dtype=torch.uint8, device=dev)
+    ninl = torch.empty((P,), dtype=torch.int32, device=dev)
+    iters = torch.empty((P,), dtype=torch.int32, device=dev)
+    status = torch.empty((P,), dtype=torch.int32, device=dev)
     nbytes = lib.fs_find_essential_workspace_bytes(P, n_max, max_iters)
     ws = _workspace(nbytes, dev, "ransac")
     _lib.check(lib.fs_find_essential_ransac(_p(mkpts0), _p(mkpts1), _p(n_corr), P, n_max, float(focal),
@@ -313,10 +313,10 @@ def recover_pose_batch(E, mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[flo
     n_corr = _chk(n_corr, torch.int32, "n_corr")
     dev = mkpts0.device
     P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
-    R = torch.zeros((P, 3, 3), dtype=torch.float64, device=dev)
-    t = torch.zeros((P, 3), dtype=torch.float64, device=dev)
-    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
-    ng = torch.zeros((P,), dtype=torch.int32, device=dev)
+    R = torch.empty((P, 3, 3), dtype=torch.float64, device=dev)
+    t = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    mask = torch.empty((P, n_max), dtype=torch.uint8, device=dev)
+    ng = torch.empty((P,), dtype=torch.int32, device=dev)
     _lib.check(lib.fs_recover_pose(_p(E), _p(mkpts0), _p(mkpts1), _p(n_corr), _p(status), P, n_max,
                                    float(focal), float(pp[0]), float(pp[1]), float(distance_thresh), _p(R),
                                    _p(t), _p(mask), _p(ng), _stream()), "fs_recover_pose")
@@ -378,13 +378,13 @@ def solve_pnp_ransac_batch(points3d, pts2d, n_corr, *, camera: ForestCamera = Fo
     n_corr = _chk(n_corr, torch.int32, "n_corr")
     dev = points3d.device
     P, n_max = int(points3d.shape[0]), int(points3d.shape[1])
-    rvec = torch.zeros((P, 3), dtype=torch.float64, device=dev)
-    tvec = torch.zeros((P, 3), dtype=torch.float64, device=dev)
-    mask = torch.zeros((P, n_max), dtype=torch.uint8, device=dev)
-    idx = torch.zeros((P, n_max), dtype=torch.int32, device=dev)
-    ninl = torch.zeros((P,), dtype=torch.int32, device=dev)
-    iters = torch.zeros((P,), dtype=torch.int32, device=dev)
-    status = torch.zeros((P,), dtype=torch.int32, device=dev)
+    rvec = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    tvec = torch.empty((P, 3), dtype=torch.float64, device=dev)
+    mask = torch.empty((P, n_max), dtype=torch.uint8, device=dev)
+    idx = torch.empty((P, n_max), dtype=torch.int32, device=dev)   # first n_inliers[p] entries are valid
+    ninl = torch.empty((P,), dtype=torch.int32, device=dev)
+    iters = torch.empty((P,), dtype=torch.int32, device=dev)
+    status = torch.empty((P,), dtype=torch.int32, device=dev)
     cam = camera.as_struct()
     nbytes = lib.fs_solve_pnp_workspace_bytes(P, n_max, max_iters)
     ws = _workspace(nbytes, dev, "ransac")

@@ -42,6 +42,20 @@ inline int check_cuda(cudaError_t e, const char* what) {
 
 inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
+// Opt a kernel into `bytes` of dynamic shared memory.  The attribute is sticky per device, so it is only raised when a
+// larger request arrives: after warm-up no call is made, which keeps the launch sequence capturable in a CUDA graph.
+// (Per-device bookkeeping: one slot per CUDA device, 64 is far above any single node.)
+template <class K>
+inline int ensure_dyn_smem(K kernel, int* granted /* [64], zero-initialised static */, size_t bytes) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if ((int)bytes <= granted[dev]) return FS_OK;
+    int s = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes),
+                       "cudaFuncSetAttribute(MaxDynamicSharedMemorySize)");
+    if (s == FS_OK) granted[dev] = (int)bytes;
+    return s;
+}
+
 int sm_count();
 void count_launch();  // every kernel launch of the library bumps fs_launch_count()
 

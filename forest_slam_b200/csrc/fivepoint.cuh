@@ -41,43 +41,52 @@ CVM_HD Cplx cdiv(Cplx a, Cplx b) {
     return {(a.re * b.re + a.im * b.im) * t, (-a.re * b.im + a.im * b.re) * t};
 }
 
-// cv::solvePoly for a real polynomial of degree <= 10, coeffs[k] multiplies z^k.  Returns the degree n
-// actually solved (leading coefficients <= DBL_EPSILON are dropped as OpenCV does); roots[0..n-1].
-CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
-    int n = 10;
-    for (; n > 1; n--)
-        if (fabs(coeffs[n]) > DBL_EPSILON) break;
-    Cplx p = {1, 0};
-    const Cplx r = {1, 1};
-    for (int i = 0; i < n; i++) {
-        roots[i] = p;
-        p = cmul(p, r);
+// One Durand-Kerner run for a fixed degree N (cv::solvePoly's loop): Gauss-Seidel updates in slot order, start
+// (1+i)^k.  Fully unrolled for N known at compile time so that the roots live in registers and the independent
+// numerator (Horner) chains of all slots can overlap the serial denominator chain; the arithmetic of every update is
+// performed in exactly OpenCV's order.  OpenCV always runs 300 sweeps; the iterates reach their rounding floor long
+// before and then only jitter in the last bits, so the sweep loop stops once the largest update stalls.
+template <int N>
+CVM_HD void dk_run(const double* coeffs, Cplx* roots, int max_iters) {
+    Cplx r[N];
+    {
+        Cplx p = {1, 0};
+        const Cplx q = {1, 1};
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            r[i] = p;
+            p = cmul(p, q);
+        }
     }
     double prev = DBL_MAX;
     int stalled = 0;
     for (int iter = 0; iter < max_iters; iter++) {
         double max_diff = 0;
-        for (int i = 0; i < n; i++) {
-            p = roots[i];
-            Cplx num = {coeffs[n], 0}, denom = {coeffs[n], 0};
-            for (int j = 0; j < n; j++) {
+#pragma unroll
+        for (int i = 0; i < N; i++) {
+            const Cplx p = r[i];
+            Cplx num = {coeffs[N], 0}, denom = {coeffs[N], 0};
+#pragma unroll
+            for (int j = 0; j < N; j++) {
                 num = cmul(num, p);
-                num.re += coeffs[n - j - 1];
+                num.re += coeffs[N - j - 1];
                 if (j != i) {
-                    const Cplx d = {p.re - roots[j].re, p.im - roots[j].im};
-                    if (d.re != 0 || d.im != 0) denom = cmul(denom, d);
-                    // coincident iterates (OpenCV's multiple-root branch) do not occur for generic data;
-                    // the factor is skipped like OpenCV does before its special-case correction
+                    const Cplx d = {p.re - r[j].re, p.im - r[j].im};
+                    // coincident iterates (OpenCV's multiple-root branch) do not occur for generic data; the factor
+                    // is skipped like OpenCV does before its special-case correction
+                    const Cplx nd = cmul(denom, d);
+                    const bool nz = d.re != 0 || d.im != 0;
+                    denom.re = nz ? nd.re : denom.re;
+                    denom.im = nz ? nd.im : denom.im;
                 }
             }
             num = cdiv(num, denom);
-            roots[i].re = p.re - num.re;
-            roots[i].im = p.im - num.im;
+            r[i].re = p.re - num.re;
+            r[i].im = p.im - num.im;
             max_diff = fmax(max_diff, sqrt(num.re * num.re + num.im * num.im));
         }
         if (max_diff <= 0) break;
-        // OpenCV keeps sweeping until iteration 300; once the quadratic convergence has hit the rounding
-        // floor the iterates only jitter by that floor.  Stop after two stalled sweeps below 1e-8.
+        // stop after two stalled sweeps below 1e-8 (quadratic convergence has hit the rounding floor)
         if (max_diff < 1e-8 && max_diff >= 0.5 * prev) {
             if (++stalled >= 2) break;
         } else {
@@ -85,8 +94,31 @@ CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
         }
         prev = max_diff;
     }
-    for (int i = 0; i < n; i++)
-        if (fabs(roots[i].im) < 1e-100) roots[i].im = 0;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+        if (fabs(r[i].im) < 1e-100) r[i].im = 0;
+        roots[i] = r[i];
+    }
+}
+
+// cv::solvePoly for a real polynomial of degree <= 10, coeffs[k] multiplies z^k.  Returns the degree n
+// actually solved (leading coefficients <= DBL_EPSILON are dropped as OpenCV does); roots[0..n-1].
+CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
+    int n = 10;
+    for (; n > 1; n--)
+        if (fabs(coeffs[n]) > DBL_EPSILON) break;
+    switch (n) {
+        case 10: dk_run<10>(coeffs, roots, max_iters); break;
+        case 9: dk_run<9>(coeffs, roots, max_iters); break;
+        case 8: dk_run<8>(coeffs, roots, max_iters); break;
+        case 7: dk_run<7>(coeffs, roots, max_iters); break;
+        case 6: dk_run<6>(coeffs, roots, max_iters); break;
+        case 5: dk_run<5>(coeffs, roots, max_iters); break;
+        case 4: dk_run<4>(coeffs, roots, max_iters); break;
+        case 3: dk_run<3>(coeffs, roots, max_iters); break;
+        case 2: dk_run<2>(coeffs, roots, max_iters); break;
+        default: dk_run<1>(coeffs, roots, max_iters); break;
+    }
     return n;
 }
 

@@ -334,7 +334,11 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
     int32_t* idx1 = ws.take<int32_t>(n);
     unsigned long long* col_best = ws.take<unsigned long long>(n);
     FS_CUDA(cudaMemsetAsync(col_best, 0, n * sizeof(unsigned long long), stream));
-    FS_CUDA(cudaFuncSetAttribute(k_float_match_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_float_match_tc, granted, (size_t)(TC_SMEM_BYTES));
+        if (st_ != FS_OK) return st_;
+    }
     for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
         const int np = min(65535, n_pairs - p0);
         const size_t o = (size_t)p0 * n_max;

@@ -131,28 +131,38 @@ k_essential_ransac(const float* __restrict__ mkpts0, const float* __restrict__ m
             }
         }
         __syncthreads();
-        // ---- solve: one thread per iteration of the round
-        if (tid < ER_CHUNK) {
-            int cnt = 0;
-            if (tid < round) {
-                double q1[5][2], q2[5][2];
-                for (int i = 0; i < 5; i++) {
-                    const int k = sh.subsets[tid][i];
-                    q1[i][0] = px1[k]; q1[i][1] = py1[k];
-                    q2[i][0] = px2[k]; q2[i][1] = py2[k];
+        // ---- solve: one thread per iteration of the round.  The solver is a long serial fp64 chain (latency bound),
+        // so the 32 solves are spread over all 8 warps (4 lanes each): every SM sub-partition interleaves two
+        // independent instruction streams instead of idling behind one warp.
+        {
+            constexpr int LANES = ER_CHUNK / ER_WARPS;  // 4
+            if (lane < LANES) {
+                const int s = warp * LANES + lane;
+                int cnt = 0;
+                if (s < round) {
+                    double q1[5][2], q2[5][2];
+                    for (int i = 0; i < 5; i++) {
+                        const int k = sh.subsets[s][i];
+                        q1[i][0] = px1[k]; q1[i][1] = py1[k];
+                        q2[i][0] = px2[k]; q2[i][1] = py2[k];
+                    }
+                    cnt = cvm::five_point(q1, q2, models + (size_t)s * ER_MAXMODELS * 9);
                 }
-                cnt = cvm::five_point(q1, q2, models + (size_t)tid * ER_MAXMODELS * 9);
+                sh.nmodels[s] = cnt;
             }
-            sh.nmodels[tid] = cnt;
+        }
+        __syncthreads();
+        if (warp == 0) {
             // exclusive prefix of model counts -> flat hypothesis list
+            const int cnt = sh.nmodels[lane];
             int incl = cnt;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int v = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += v;
             }
-            sh.hyp_offset[tid] = incl - cnt;
-            if (tid == 31) sh.hyp_offset[32] = incl;
+            sh.hyp_offset[lane] = incl - cnt;
+            if (lane == 31) sh.hyp_offset[32] = incl;
         }
         __syncthreads();
         // ---- score: one warp per hypothesis
@@ -309,7 +319,11 @@ extern "C" int fs_find_essential_ransac(const float* mkpts0, const float* mkpts1
     FS_REQUIRE(focal != 0, "focal must be non-zero");
     const size_t smem = er_smem_bytes(n_max);
     FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~6200)");
-    FS_CUDA(cudaFuncSetAttribute(k_essential_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_essential_ransac, granted, (size_t)((int)smem));
+        if (st_ != FS_OK) return st_;
+    }
     k_essential_ransac<<<n_pairs, ER_THREADS, smem, (cudaStream_t)stream>>>(
         mkpts0, mkpts1, n_corr, n_max, focal, pp_x, pp_y, prob, threshold, max_iters, E, mask, n_inliers, iters_run,
         status);
@@ -336,7 +350,11 @@ extern "C" int fs_score_essential(const float* mkpts0, const float* mkpts1, cons
     FS_REQUIRE(mkpts0 && mkpts1 && n_corr && models_E && counts, "null pointer");
     const size_t smem = (size_t)n_max * 4 * sizeof(double);
     FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging");
-    FS_CUDA(cudaFuncSetAttribute(k_score_essential, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_score_essential, granted, (size_t)((int)smem));
+        if (st_ != FS_OK) return st_;
+    }
     dim3 grid((n_hyp + SC_HYP_PER_CTA - 1) / SC_HYP_PER_CTA, n_pairs);
     k_score_essential<<<grid, SC_THREADS, smem, (cudaStream_t)stream>>>(mkpts0, mkpts1, n_corr, n_max, focal, pp_x,
                                                                       pp_y, threshold, models_E, n_hyp, counts);

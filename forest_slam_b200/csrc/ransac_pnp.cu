@@ -82,15 +82,17 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
 
 
 // ------------------------------------------------------------------------------------------------ A7 RANSAC
-// One CTA per frame pair, rounds of 32 RANSAC iterations (same structure as k_essential_ransac):
+// One CTA per frame pair, rounds of PR_CHUNK RANSAC iterations (same structure as k_essential_ransac):
 //   sample : thread 0 replays cv::RNG(2^64-1) (RANSACPointSetRegistrator::getSubset);
-//   solve  : 32 threads, one EPnP-on-5-points each (epnp.cuh) -> model (rvec | tvec) in shared memory;
+//   solve  : PR_CHUNK threads spread over all warps, one EPnP-on-5-points each (epnp.cuh) -> model (rvec | tvec) in
+//            shared memory;
 //   score  : ONE WARP PER HYPOTHESIS over all correspondences staged in shared memory: projectPoints with the
 //            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, ballot/popc count;
 //   select : thread 0 walks the counts in OpenCV's serial order (strictly greater, adaptive iteration cap).
 constexpr int PR_THREADS = 256;
 constexpr int PR_WARPS = PR_THREADS / 32;
-constexpr int PR_CHUNK = 32;
+constexpr int PR_CHUNK = 128;  // speculative iterations per round: the EPnP solves are latency bound, so a round of 128
+                               // (16 lanes x 8 warps) costs about as much as a round of 32 and cuts the number of rounds by 4
 
 struct PRShared {
     double models[PR_CHUNK][6];
@@ -180,17 +182,19 @@ k_pnp_ransac(const float* __restrict__ points3d, const float* __restrict__ pts2d
             }
         }
         __syncthreads();
-        if (tid < round) {
+        // the minimal solver is a long serial fp64 chain: spread the 32 solves over all 8 warps (4 lanes each)
+        const int sidx = warp * (PR_CHUNK / PR_WARPS) + lane;
+        if (lane < PR_CHUNK / PR_WARPS && sidx < round) {
             double obj[5][3];
             float img[5][2];
             for (int i = 0; i < 5; i++) {
-                const int k = sh.subsets[tid][i];
+                const int k = sh.subsets[sidx][i];
                 obj[i][0] = st.X[k]; obj[i][1] = st.Y[k]; obj[i][2] = st.Z[k];
                 img[i][0] = st.u[k]; img[i][1] = st.v[k];
             }
             double m[6];
             cvm::pnp_minimal_epnp5(cam, obj, img, m);
-            for (int i = 0; i < 6; i++) sh.models[tid][i] = m[i];
+            for (int i = 0; i < 6; i++) sh.models[sidx][i] = m[i];
         }
         __syncthreads();
         for (int h = warp; h < round; h += PR_WARPS) {
@@ -498,7 +502,11 @@ extern "C" int fs_score_pnp(const float* points3d, const float* pts2d, const int
     FS_REQUIRE(points3d && pts2d && n_corr && cam && models_rt && counts, "null pointer");
     const size_t smem = PnPStage::bytes(n_max);
     FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging");
-    FS_CUDA(cudaFuncSetAttribute(k_score_pnp, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_score_pnp, granted, (size_t)((int)smem));
+        if (st_ != FS_OK) return st_;
+    }
     dim3 grid((n_hyp + PS_HYP_PER_CTA - 1) / PS_HYP_PER_CTA, n_pairs);
     k_score_pnp<<<grid, PS_THREADS, smem, (cudaStream_t)stream>>>(points3d, pts2d, n_corr, n_max, *cam, reproj_error,
                                                                 models_rt, n_hyp, counts);
@@ -531,7 +539,11 @@ extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, co
     double* model = ws.take<double>((size_t)n_pairs * 6);
     const size_t smem = fs::align_up(PnPStage::bytes(n_max), 16) + sizeof(PRShared) + 16;
     FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~7000)");
-    FS_CUDA(cudaFuncSetAttribute(k_pnp_ransac, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_pnp_ransac, granted, (size_t)((int)smem));
+        if (st_ != FS_OK) return st_;
+    }
     k_pnp_ransac<<<n_pairs, PR_THREADS, smem, stream>>>(points3d, pts2d, n_corr, n_max, *cam, reproj_error, confidence,
                                                        max_iters, min_points, model, mask, inlier_idx, n_inliers,
                                                        iters_run, status);

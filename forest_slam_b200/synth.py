@@ -102,7 +102,7 @@ def make_trajectory(n_frames: int, seed: int = SEED0, step: float = 0.13, z0: fl
 def observe(world: ForestWorld, T_wc: np.ndarray, n_kpts: int, frame_seed: int,
             cam: ForestCamera = ForestCamera(), spurious: float = 0.25, pix_sigma: float = 0.5,
             bit_flip: float = 0.06, f32_sigma: float = 0.05, zmin: float = 1.0, zmax: float = 60.0,
-            border: int = 4) -> Frame:
+            border: int = 4, pos_outlier: float = 0.0) -> Frame:
     rng = np.random.default_rng(frame_seed)
     T_cw = np.linalg.inv(T_wc)
     P = world.points @ T_cw[:3, :3].T + T_cw[:3, 3]
@@ -116,6 +116,12 @@ def observe(world: ForestWorld, T_wc: np.ndarray, n_kpts: int, frame_seed: int,
     sel = vis[np.argsort(world.priority[vis], kind="stable")[:n_true]]
     n_spur = n_kpts - n_true
     kp = np.stack([u[sel], v[sel]], axis=-1) + rng.normal(0, pix_sigma, (n_true, 2))
+    if pos_outlier > 0:
+        # gross mismatches: the descriptor still matches but the keypoint sits somewhere else (~20 % of the
+        # matches of the RANSAC benchmarks are corrupted so that the outlier ratio is ~0.3)
+        bad = rng.random(n_true) < pos_outlier
+        kp[bad, 0] = rng.uniform(border, cam.width - border, int(bad.sum()))
+        kp[bad, 1] = rng.uniform(border, cam.height - border, int(bad.sum()))
     kp[:, 0] = np.clip(kp[:, 0], 0.0, cam.width - 1.001)
     kp[:, 1] = np.clip(kp[:, 1], 0.0, cam.height - 1.001)
     disp = cam.fx * cam.baseline / z[sel] + rng.normal(0, 0.1, n_true)
