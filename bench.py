@@ -377,8 +377,7 @@ def run_b200(args):
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     t_dev, t_e2e = float(tt[0]), float(tt[1])
     if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
+        _finish(world)
         return
 
     total_pairs = P * world * args.steps
@@ -426,8 +425,22 @@ def run_b200(args):
                                 "sample": f"{n} frame pairs of this workload in {dt:.1f} s, {procs} processes x 1 "
                                           f"library thread, cv2 {cv2.__version__} + torch CPU literal calls"}
     print(json.dumps(line), flush=True)
+    _finish(world)
+
+
+def _finish(world: int):
+    """Leave without tearing the NCCL communicator down: destroy_process_group() can block forever when collectives
+    of that communicator live inside captured CUDA graphs.  All ranks meet at a barrier first, so nobody is killed
+    mid-collective; stdout is already flushed."""
     if world > 1:
-        dist.destroy_process_group()
+        import torch
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def main():
