@@ -317,9 +317,10 @@ def recover_pose_batch(E, mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[flo
     t = torch.empty((P, 3), dtype=torch.float64, device=dev)
     mask = torch.empty((P, n_max), dtype=torch.uint8, device=dev)
     ng = torch.empty((P,), dtype=torch.int32, device=dev)
+    ws = _workspace(lib.fs_recover_pose_workspace_bytes(P), dev, "recover_pose")
     _lib.check(lib.fs_recover_pose(_p(E), _p(mkpts0), _p(mkpts1), _p(n_corr), _p(status), P, n_max,
                                    float(focal), float(pp[0]), float(pp[1]), float(distance_thresh), _p(R),
-                                   _p(t), _p(mask), _p(ng), _stream()), "fs_recover_pose")
+                                   _p(t), _p(mask), _p(ng), _p(ws), ws.numel(), _stream()), "fs_recover_pose")
     return {"R": R, "t": t, "mask": mask, "n_good": ng}
 
 

@@ -41,86 +41,248 @@ CVM_HD Cplx cdiv(Cplx a, Cplx b) {
     return {(a.re * b.re + a.im * b.im) * t, (-a.re * b.im + a.im * b.re) * t};
 }
 
-// One Durand-Kerner run for a fixed degree N (cv::solvePoly's loop): Gauss-Seidel updates in slot order, start
-// (1+i)^k.  Fully unrolled for N known at compile time so that the roots live in registers and the independent
-// numerator (Horner) chains of all slots can overlap the serial denominator chain; the arithmetic of every update is
-// performed in exactly OpenCV's order.  OpenCV always runs 300 sweeps; the iterates reach their rounding floor long
-// before and then only jitter in the last bits, so the sweep loop stops once the largest update stalls.
+#ifdef FS_PROFILE_FIVEPOINT  // scratch/ micro-benchmarks only: cycle stamps between the solver's stages
+#ifdef __CUDA_ARCH__
+#define FP_TICK(k) fp_prof[k] = clock64()
+#define FP_SWEEPS(n) atomicAdd(&fp_sweeps[(n) < 511 ? (n) : 511], 1)
+#else
+#define FP_TICK(k)
+#define FP_SWEEPS(n)
+#endif
+__device__ long long fp_prof[8];
+__device__ int fp_sweeps[512];  // histogram of Durand-Kerner sweeps
+#else
+#define FP_TICK(k)
+#define FP_SWEEPS(n)
+#endif
+// exact "both components are +-0" test on the integer pipe (the fp64 pipe is the scarce resource of this solver)
+CVM_HD bool cplx_is_zero(Cplx d) {
+#ifdef __CUDA_ARCH__
+    return (((unsigned long long)__double_as_longlong(d.re) | (unsigned long long)__double_as_longlong(d.im)) << 1) == 0;
+#else
+    return d.re == 0 && d.im == 0;
+#endif
+}
+
+// Durand-Kerner state of one polynomial: roots + the stop-rule bookkeeping, so that a run can be suspended after a
+// sweep budget and resumed elsewhere (ransac_essential.cu hands the rare slow cases to a warp-cooperative tail).
+struct DKState {
+    Cplx r[10];
+    double floor_md;
+    int n;        // degree being solved
+    int iter;     // sweeps done
+    int stalled;
+    int done;
+};
+
+// Stop rule.  OpenCV always runs 300 sweeps; the iterates reach their rounding floor after ~20 and from then on only
+// jitter in the last bits (very often an exact 2-cycle).  A run stops once the largest update is below 1e-8 and has
+// failed twice in a row to halve the smallest update seen so far, and only after an EVEN number of sweeps so that an
+// exact 2-cycle is left in the phase OpenCV's 300th sweep leaves it in.  Returns true when the run is over.
+CVM_HD bool dk_stop_rule(double max_diff, int iter /* index of the sweep just done */, double& floor_md, int& stalled) {
+    if (max_diff <= 0) return true;
+    if (max_diff < 1e-8 && max_diff >= 0.5 * floor_md) stalled++;
+    else stalled = 0;
+    floor_md = fmin(floor_md, max_diff);
+    return stalled >= 2 && (iter & 1);
+}
+
+// Sweeps of cv::solvePoly's Durand-Kerner loop for a fixed degree N: Gauss-Seidel updates in slot order, start
+// (1+i)^k, every update in exactly OpenCV's operation order.  Fully unrolled for N known at compile time so that the
+// roots live in registers.  Runs until the stop rule fires or `until_iter` sweeps have been done in total.
 template <int N>
-CVM_HD void dk_run(const double* coeffs, Cplx* roots, int max_iters) {
+CVM_HD void dk_run(const double* coeffs, DKState& st, int until_iter) {
     Cplx r[N];
-    {
-        Cplx p = {1, 0};
-        const Cplx q = {1, 1};
 #pragma unroll
-        for (int i = 0; i < N; i++) {
-            r[i] = p;
-            p = cmul(p, q);
+    for (int i = 0; i < N; i++) r[i] = st.r[i];
+    double floor_md = st.floor_md;
+    int stalled = st.stalled, iter = st.iter;
+    bool done = false;
+    for (; iter < until_iter && !done; iter++) {
+        // numerators P(r_i): root i still holds its pre-update value when OpenCV evaluates it, so all N Horner chains
+        // are independent of this sweep's updates and are advanced in lock-step (same operations per chain)
+        Cplx num[N];
+#pragma unroll
+        for (int i = 0; i < N; i++) num[i] = {coeffs[N], 0};
+#pragma unroll
+        for (int j = 0; j < N; j++) {
+#pragma unroll
+            for (int i = 0; i < N; i++) {
+                num[i] = cmul(num[i], r[i]);
+                num[i].re += coeffs[N - j - 1];
+            }
         }
-    }
-    double prev = DBL_MAX;
-    int stalled = 0;
-    for (int iter = 0; iter < max_iters; iter++) {
-        double max_diff = 0;
+        double max_sq = 0;
 #pragma unroll
         for (int i = 0; i < N; i++) {
             const Cplx p = r[i];
-            Cplx num = {coeffs[N], 0}, denom = {coeffs[N], 0};
+            Cplx denom = {coeffs[N], 0};
+            bool coincident = false;
 #pragma unroll
             for (int j = 0; j < N; j++) {
-                num = cmul(num, p);
-                num.re += coeffs[N - j - 1];
                 if (j != i) {
                     const Cplx d = {p.re - r[j].re, p.im - r[j].im};
-                    // coincident iterates (OpenCV's multiple-root branch) do not occur for generic data; the factor
-                    // is skipped like OpenCV does before its special-case correction
-                    const Cplx nd = cmul(denom, d);
-                    const bool nz = d.re != 0 || d.im != 0;
-                    denom.re = nz ? nd.re : denom.re;
-                    denom.im = nz ? nd.im : denom.im;
+                    coincident |= cplx_is_zero(d);
+                    denom = cmul(denom, d);
                 }
             }
-            num = cdiv(num, denom);
-            r[i].re = p.re - num.re;
-            r[i].im = p.im - num.im;
-            max_diff = fmax(max_diff, sqrt(num.re * num.re + num.im * num.im));
+            if (coincident) {
+                // coincident iterates (OpenCV's multiple-root branch) do not occur for generic data; the zero factors
+                // are skipped like OpenCV does before its special-case correction
+                denom = {coeffs[N], 0};
+#pragma unroll
+                for (int j = 0; j < N; j++) {
+                    if (j != i) {
+                        const Cplx d = {p.re - r[j].re, p.im - r[j].im};
+                        if (!cplx_is_zero(d)) denom = cmul(denom, d);
+                    }
+                }
+            }
+            const Cplx q = cdiv(num[i], denom);
+            r[i].re = p.re - q.re;
+            r[i].im = p.im - q.im;
+            max_sq = fmax(max_sq, q.re * q.re + q.im * q.im);
         }
-        if (max_diff <= 0) break;
-        // stop after two stalled sweeps below 1e-8 (quadratic convergence has hit the rounding floor)
-        if (max_diff < 1e-8 && max_diff >= 0.5 * prev) {
-            if (++stalled >= 2) break;
-        } else {
-            stalled = 0;
-        }
-        prev = max_diff;
+        // max_i sqrt(m_i) == sqrt(max_i m_i): sqrt is correctly rounded, hence monotone
+        const double max_diff = sqrt(max_sq);
+#ifdef FP_DK_TRACE
+        FP_DK_TRACE(iter, max_diff, r);
+#endif
+        done = dk_stop_rule(max_diff, iter, floor_md, stalled);
     }
 #pragma unroll
-    for (int i = 0; i < N; i++) {
-        if (fabs(r[i].im) < 1e-100) r[i].im = 0;
-        roots[i] = r[i];
-    }
+    for (int i = 0; i < N; i++) st.r[i] = r[i];
+    st.floor_md = floor_md;
+    st.stalled = stalled;
+    st.iter = iter;
+    st.done = (done || iter >= 300) ? 1 : 0;
 }
 
-// cv::solvePoly for a real polynomial of degree <= 10, coeffs[k] multiplies z^k.  Returns the degree n
-// actually solved (leading coefficients <= DBL_EPSILON are dropped as OpenCV does); roots[0..n-1].
-CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
+// cv::solvePoly for a real polynomial of degree <= 10, coeffs[k] multiplies z^k: start state.  The degree actually
+// solved drops leading coefficients <= DBL_EPSILON as OpenCV does.
+CVM_HD void dk_init(const double* coeffs, DKState& st) {
     int n = 10;
     for (; n > 1; n--)
         if (fabs(coeffs[n]) > DBL_EPSILON) break;
-    switch (n) {
-        case 10: dk_run<10>(coeffs, roots, max_iters); break;
-        case 9: dk_run<9>(coeffs, roots, max_iters); break;
-        case 8: dk_run<8>(coeffs, roots, max_iters); break;
-        case 7: dk_run<7>(coeffs, roots, max_iters); break;
-        case 6: dk_run<6>(coeffs, roots, max_iters); break;
-        case 5: dk_run<5>(coeffs, roots, max_iters); break;
-        case 4: dk_run<4>(coeffs, roots, max_iters); break;
-        case 3: dk_run<3>(coeffs, roots, max_iters); break;
-        case 2: dk_run<2>(coeffs, roots, max_iters); break;
-        default: dk_run<1>(coeffs, roots, max_iters); break;
+    st.n = n;
+    Cplx p = {1, 0};
+    const Cplx q = {1, 1};
+    for (int i = 0; i < 10; i++) {
+        st.r[i] = p;
+        p = cmul(p, q);
     }
-    return n;
+    st.floor_md = DBL_MAX;
+    st.iter = 0;
+    st.stalled = 0;
+    st.done = 0;
 }
+
+// advance until the stop rule fires or `until_iter` total sweeps (OpenCV's cap is 300)
+CVM_HD void dk_advance(const double* coeffs, DKState& st, int until_iter) {
+    switch (st.n) {
+        case 10: dk_run<10>(coeffs, st, until_iter); break;
+        case 9: dk_run<9>(coeffs, st, until_iter); break;
+        case 8: dk_run<8>(coeffs, st, until_iter); break;
+        case 7: dk_run<7>(coeffs, st, until_iter); break;
+        case 6: dk_run<6>(coeffs, st, until_iter); break;
+        case 5: dk_run<5>(coeffs, st, until_iter); break;
+        case 4: dk_run<4>(coeffs, st, until_iter); break;
+        case 3: dk_run<3>(coeffs, st, until_iter); break;
+        case 2: dk_run<2>(coeffs, st, until_iter); break;
+        default: dk_run<1>(coeffs, st, until_iter); break;
+    }
+}
+
+// roots in slot order once a run is over (OpenCV zeroes negligible imaginary parts)
+CVM_HD int dk_finish(DKState& st, Cplx* roots) {
+    FP_SWEEPS(st.iter);
+    for (int i = 0; i < st.n; i++) {
+        if (fabs(st.r[i].im) < 1e-100) st.r[i].im = 0;
+        roots[i] = st.r[i];
+    }
+    return st.n;
+}
+
+CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
+    DKState st;
+    dk_init(coeffs, st);
+    dk_advance(coeffs, st, max_iters);
+    return dk_finish(st, roots);
+}
+
+#ifdef __CUDACC__
+// Warp-cooperative continuation of a suspended run: lane i owns root i.  The arithmetic of every root update is the
+// scalar loop's, operation for operation (numerator Horner chain, denominator factors in slot order with the roots
+// already updated in this sweep, complex division), so a run finished here ends in exactly the state the scalar loop
+// would have reached; what changes is the critical path of a sweep: the N numerators and all "already updated"
+// denominator factors are evaluated side by side, leaving sum_i (N - i) dependent complex products per sweep instead
+// of ~2 N^2 issued from one thread.  All 32 lanes must call.
+__device__ inline void dk_advance_warp(const double* coeffs, DKState& st, int until_iter) {
+    const int lane = threadIdx.x & 31;
+    const int N = st.n;
+    const unsigned full = 0xffffffffu;
+    Cplx r = st.r[lane < 10 ? lane : 0];
+    double floor_md = st.floor_md;
+    int stalled = st.stalled, iter = st.iter;
+    bool done = false;
+    for (; iter < until_iter && !done; iter++) {
+        Cplx num = {coeffs[N], 0};
+        for (int j = 0; j < N; j++) {
+            num = cmul(num, r);
+            num.re += coeffs[N - j - 1];
+        }
+        const Cplx p = r;
+        Cplx ro[10];  // every slot's pre-sweep value
+#pragma unroll
+        for (int j = 0; j < 10; j++) {
+            ro[j].re = __shfl_sync(full, r.re, j);
+            ro[j].im = __shfl_sync(full, r.im, j);
+        }
+        Cplx denom = {coeffs[N], 0};  // factors of slots already updated in this sweep, absorbed as they appear
+        double mag2 = 0;
+        // Always 10 steps and no shuffle under a branch (a shuffle the compiler cannot prove convergent costs a
+        // warp-sync sequence): slots >= N only produce values nobody reads.
+#pragma unroll
+        for (int i = 0; i < 10; i++) {
+            // slot i: remaining factors (slots j > i, still at their pre-sweep values), then the update
+            Cplx dch = denom;
+#pragma unroll
+            for (int j = i + 1; j < 10; j++) {
+                const Cplx d = {p.re - ro[j].re, p.im - ro[j].im};
+                const Cplx nd = cmul(dch, d);
+                const bool nz = (d.re != 0 || d.im != 0) && j < N;
+                dch.re = nz ? nd.re : dch.re;
+                dch.im = nz ? nd.im : dch.im;
+            }
+            const Cplx q = cdiv(num, dch);
+            const Cplx nr = {p.re - q.re, p.im - q.im};
+            const double bre = __shfl_sync(full, nr.re, i), bim = __shfl_sync(full, nr.im, i);
+            const Cplx d = {p.re - bre, p.im - bim};
+            const Cplx nd = cmul(denom, d);
+            const bool absorb = lane > i && (d.re != 0 || d.im != 0);
+            denom.re = absorb ? nd.re : denom.re;
+            denom.im = absorb ? nd.im : denom.im;
+            const bool mine = lane == i;
+            r.re = mine ? nr.re : r.re;
+            r.im = mine ? nr.im : r.im;
+            mag2 = mine ? q.re * q.re + q.im * q.im : mag2;
+        }
+        double max_diff = lane < N ? sqrt(mag2) : 0.0;
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) max_diff = fmax(max_diff, __shfl_xor_sync(full, max_diff, o));
+        done = __any_sync(full, dk_stop_rule(max_diff, iter, floor_md, stalled));  // (uniform; the vote tells the compiler)
+    }
+#pragma unroll
+    for (int j = 0; j < 10; j++) {
+        const double re = __shfl_sync(full, r.re, j), im = __shfl_sync(full, r.im, j);
+        if (j < N) st.r[j] = {re, im};
+    }
+    st.floor_md = floor_md;
+    st.stalled = stalled;
+    st.iter = iter;
+    st.done = (done || iter >= 300) ? 1 : 0;
+}
+#endif
 
 // polynomial helpers, coefficient k multiplies z^k
 template <int NA, int NB>
@@ -129,8 +291,17 @@ CVM_HD void pmul_acc(const double* a, const double* b, double* out, double sign)
         for (int j = 0; j < NB; j++) out[i + j] += sign * (a[i] * b[j]);
 }
 
-// q1, q2: 5 normalised correspondences (x, y); models: up to 10 matrices, 9 doubles each, row-major.
-CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* models) {
+// What the stages after the polynomial need from the stages before it.
+struct FPSetup {
+    double EE[36];     // null-space basis: EE[a*9 + 3i + j], basis matrix a, entry (i, j)
+    double B[3][13];   // B(z) in OpenCV's layout
+    double coeffs[11]; // det B(z), coefficient k multiplies z^k
+};
+
+// stages 1-4: q1, q2 = 5 normalised correspondences (x, y).  Returns false when the constraint matrix is singular
+// (OpenCV's inv() returns zeros -> no usable model).
+CVM_HD bool five_point_setup(const double (*q1)[2], const double (*q2)[2], FPSetup& fs) {
+    FP_TICK(0);
     // 1-2. Q and its completed right singular basis
     double At[9 * 9], W[5], Vt[25];
     for (int i = 0; i < 5; i++) {
@@ -142,6 +313,8 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
     }
     jacobi_svd<9, 5, 9>(At, 9, W, Vt);
     const double* EE = At + 9 * 5;  // EE[a*9 + 3i + j]: basis matrix a, entry (i, j)
+    for (int k = 0; k < 36; k++) fs.EE[k] = EE[k];
+    FP_TICK(1);
 
     // 3. constraints.  Lq[s][m]: quadratic form of (E E^T - 1/2 tr(E E^T) I), symmetric index s of (i, k)
     double A[10][20];
@@ -187,34 +360,49 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
                 for (int c = 0; c < 4; c++) A[9][t3(m, c)] += cr[d][m] * EE[c * 9 + d];
     }
 
-    // Gauss-Jordan with partial pivoting on [A(:, 0:10) | A(:, 10:20)]
+    FP_TICK(2);
+    // Gauss-Jordan with partial pivoting on [A(:, 0:10) | A(:, 10:20)].  Fully unrolled: the only dynamic index is the
+    // pivot row; the row operations of one elimination step are independent of each other and pipeline freely.
+#pragma unroll
     for (int c = 0; c < 10; c++) {
         int piv = c;
         double best = fabs(A[c][c]);
-        for (int r = c + 1; r < 10; r++)
-            if (fabs(A[r][c]) > best) {
-                best = fabs(A[r][c]);
+#pragma unroll
+        for (int r = c + 1; r < 10; r++) {
+            const double v = fabs(A[r][c]);
+            if (v > best) {
+                best = v;
                 piv = r;
             }
-        if (best < DBL_MIN) return 0;  // singular: OpenCV's inv() returns zeros -> no usable model
-        if (piv != c)
-            for (int k = c; k < 20; k++) {
-                const double t = A[c][k];
-                A[c][k] = A[piv][k];
-                A[piv][k] = t;
-            }
-        const double inv = 1. / A[c][c];
-        for (int k = c; k < 20; k++) A[c][k] *= inv;
+        }
+        if (best < DBL_MIN) return false;  // singular: OpenCV's inv() returns zeros -> no usable model
+        double prow[20];
+#pragma unroll
+        for (int k = c; k < 20; k++) prow[k] = A[piv][k];
+        if (piv != c) {
+#pragma unroll
+            for (int k = c; k < 20; k++) A[piv][k] = A[c][k];
+        }
+        const double inv = 1. / prow[c];
+#pragma unroll
+        for (int k = c; k < 20; k++) {
+            prow[k] *= inv;
+            A[c][k] = prow[k];
+        }
+#pragma unroll
         for (int r = 0; r < 10; r++) {
             if (r == c) continue;
             const double f = A[r][c];
-            if (f == 0) continue;
-            for (int k = c; k < 20; k++) A[r][k] -= f * A[c][k];
+            if (f != 0) {
+#pragma unroll
+                for (int k = c; k < 20; k++) A[r][k] -= f * prow[k];
+            }
         }
     }
 
+    FP_TICK(3);
     // 4. B(z): rows (4,5), (6,7), (8,9) -> [cubic | cubic | quartic], highest power first (OpenCV layout b[13])
-    double B[3][13];
+    double (*B)[13] = fs.B;
     for (int i = 0; i < 3; i++) {
         const double* r1 = &A[4 + 2 * i][10];
         const double* r2 = &A[5 + 2 * i][10];
@@ -223,7 +411,7 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
         b[4] = -r2[3];        b[5] = r1[3] - r2[4]; b[6] = r1[4] - r2[5]; b[7] = r1[5];
         b[8] = -r2[6];        b[9] = r1[6] - r2[7]; b[10] = r1[7] - r2[8]; b[11] = r1[8] - r2[9]; b[12] = r1[9];
     }
-    double coeffs[11];
+    double* coeffs = fs.coeffs;
     {
         // ascending-power copies of the blocks
         double P[3][3][5];
@@ -250,12 +438,14 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
         pmul_acc<4, 8>(P[0][1], m1, coeffs, -1.);
         pmul_acc<5, 7>(P[0][2], m2, coeffs, 1.);
     }
+    FP_TICK(4);
+    return true;
+}
 
-    // 5. roots
-    Cplx roots[10];
-    const int n = dk_solve(coeffs, roots);
-
-    // 6. candidates in slot order
+// stage 6: candidates in root-slot order; models: up to 10 matrices, 9 doubles each, row-major
+CVM_HD int five_point_models(const FPSetup& fs, const Cplx* roots, int n, double* models) {
+    const double* EE = fs.EE;
+    const double (*B)[13] = fs.B;
     int count = 0;
     for (int i = 0; i < n; i++) {
         if (fabs(roots[i].im) > 1e-10) continue;
@@ -282,7 +472,18 @@ CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* mode
         for (int k = 0; k < 9; k++) e[k] /= nrm;
         count++;
     }
+    FP_TICK(6);
     return count;
+}
+
+// q1, q2: 5 normalised correspondences (x, y); models: up to 10 matrices, 9 doubles each, row-major.
+CVM_HD int five_point(const double (*q1)[2], const double (*q2)[2], double* models) {
+    FPSetup fs;
+    if (!five_point_setup(q1, q2, fs)) return 0;
+    Cplx roots[10];
+    const int n = dk_solve(fs.coeffs, roots);
+    FP_TICK(5);
+    return five_point_models(fs, roots, n, models);
 }
 
 // EMEstimatorCallback::computeError for one correspondence (double arithmetic in OpenCV's operation order,

@@ -1,33 +1,22 @@
-// ransac_essential.cu — A4: essential-matrix RANSAC with OpenCV's exact loop semantics, one CTA per frame
-// pair, everything (sampler, minimal solver, scoring, adaptive stop) on the device in ONE launch.
+// ransac_essential.cu — A4: essential-matrix RANSAC with OpenCV's exact loop semantics for a whole batch of frame
+// pairs, everything (sampler, minimal solver, scoring, adaptive stop) on the device.
 //
 // Replaces  E, mask = cv2.findEssentialMat(mkpts0, mkpts1, focal=K0[0,0], pp=(K0[0,2], K0[1,2]),
 //                                          method=cv2.RANSAC, prob=0.999, threshold=1.0)    mono_slam.py:111
 // (OpenCV: calib3d/five-point.cpp findEssentialMat + EMEstimatorCallback, calib3d/ptsetreg.cpp
 //  RANSACPointSetRegistrator::run / getSubset / findInliers / RANSACUpdateNumIters.)
 //
-// Structure of one CTA (256 threads, 8 warps), per round of 32 RANSAC iterations:
-//   sample : thread 0 replays cv::RNG(2^64-1) and draws the next 32 five-subsets (sequential by nature);
-//   solve  : 32 threads, one five-point solve each (fivepoint.cuh) -> <= 10 candidate E per iteration in smem;
-//   score  : ONE WARP PER HYPOTHESIS over all correspondences, which live in shared memory as normalised
-//            doubles (SoA); Sampson error in OpenCV's operation order (no FMA), cast to float32, compared
-//            with (float)thr^2, counted with ballot/popc;
-//   select : thread 0 walks the round's counts in OpenCV's sequential order (strictly-greater update,
-//            adaptive iteration cap) so that the result is the one the serial loop would have produced.
-// Work beyond the adaptive cap inside the last round is discarded, never observed.
+// Launch sequence (ransac_grid.cuh): normalise -> rounds of {select + sample, solve, score} spread over the whole
+// GPU -> finish (the winner's mask is recomputed with identical arithmetic instead of being stored per hypothesis).
+//   solve  : one thread per RANSAC iteration, Nister five-point (fivepoint.cuh) -> <= 10 candidate E;
+//   score  : ONE WARP PER HYPOTHESIS over the pair's correspondences, which live in shared memory as normalised
+//            doubles (SoA); Sampson error in OpenCV's operation order (no FMA), cast to float32, compared with
+//            (float)thr^2, counted with a warp reduction.
 #include "common.cuh"
 #include "fivepoint.cuh"
+#include "ransac_grid.cuh"
 
 namespace {
-
-constexpr int ER_THREADS = 256;
-constexpr int ER_WARPS = ER_THREADS / 32;
-constexpr int ER_CHUNK = 32;
-constexpr int ER_MAXMODELS = 10;
-
-struct SampsonE {
-    double e[9];
-};
 
 using cvm::sampson_f32;
 
@@ -39,15 +28,6 @@ __device__ __forceinline__ int warp_count_inliers(const double* E, const double*
     for (int i = lane; i < n; i += 32) cnt += sampson_f32(E, px1[i], py1[i], px2[i], py2[i]) <= thr2 ? 1 : 0;
     return __reduce_add_sync(0xffffffffu, cnt);
 }
-
-struct ERShared {
-    int nmodels[ER_CHUNK];
-    int counts[ER_CHUNK][ER_MAXMODELS];
-    int subsets[ER_CHUNK][5];
-    int hyp_offset[ER_CHUNK + 1];
-    int niters, best, done_iters, stop;
-    double bestE[9];
-};
 
 __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1, int n, double focal, double ppx,
                                              double ppy, double* px1, double* py1, double* px2, double* py2) {
@@ -62,176 +42,137 @@ __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1,
     }
 }
 
-__global__ void __launch_bounds__(ER_THREADS)
-k_essential_ransac(const float* __restrict__ mkpts0, const float* __restrict__ mkpts1,
-                   const int32_t* __restrict__ n_corr, int n_max, double focal, double ppx, double ppy,
-                   double prob, double threshold, int max_iters, double* __restrict__ E_out,
-                   uint8_t* __restrict__ mask_out, int32_t* __restrict__ n_inliers,
-                   int32_t* __restrict__ iters_run, int32_t* __restrict__ status) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    double* px1 = reinterpret_cast<double*>(smem_raw);
-    double* py1 = px1 + n_max;
-    double* px2 = py1 + n_max;
-    double* py2 = px2 + n_max;
-    double* models = py2 + n_max;  // [ER_CHUNK][ER_MAXMODELS][9]
-    ERShared& sh = *reinterpret_cast<ERShared*>(models + ER_CHUNK * ER_MAXMODELS * 9);
-
-    const int p = blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = min(n_corr[p], n_max);
-    uint8_t* mask = mask_out + (size_t)p * n_max;
-    double* Eo = E_out + 9 * (size_t)p;
-
-    if (n < 5) {  // cv2 returns (None, None): RANSACPointSetRegistrator::run -> count < modelPoints
-        for (int i = tid; i < n_max; i += ER_THREADS) mask[i] = 0;
-        if (tid < 9) Eo[tid] = 0.0;
-        if (tid == 0) {
-            n_inliers[p] = 0;
-            if (iters_run) iters_run[p] = 0;
-            status[p] = FS_PAIR_TOO_FEW;
-        }
-        return;
+// ------------------------------------------------------------------------------------------------ engine policy
+struct EPolicy {
+    static constexpr int MP = 5;     // model points
+    static constexpr int MAXM = 10;  // candidate models per sample
+    static constexpr int MD = 9;     // doubles per model
+    struct Params {
+        const double* pts;  // [n_pairs][4][n_max]: x1 | y1 | x2 | y2, normalised
+        int n_max;
+        float thr2;
+    };
+    static size_t stage_bytes(int n_max) { return (size_t)n_max * 4 * sizeof(double); }
+    __device__ static void stage(const Params& prm, int p, int n, unsigned char* smem) {
+        double* dst = reinterpret_cast<double*>(smem);
+        const double* src = prm.pts + (size_t)p * 4 * prm.n_max;
+        for (int c = 0; c < 4; c++)
+            for (int i = threadIdx.x; i < n; i += blockDim.x) dst[c * prm.n_max + i] = src[c * prm.n_max + i];
     }
-    stage_points(mkpts0 + 2 * (size_t)p * n_max, mkpts1 + 2 * (size_t)p * n_max, n, focal, ppx, ppy, px1, py1,
-                 px2, py2);
-    double thr = threshold / ((focal + focal) / 2);
-    const float thr2 = (float)(thr * thr);
-
-    cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);  // RNG rng((uint64)-1) inside run(); only thread 0 advances it
-    if (tid == 0) {
-        sh.niters = max(max_iters, 1);
-        sh.best = 0;
-        sh.done_iters = 0;
-        sh.stop = 0;
-    }
-    __syncthreads();
-
-    for (int base = 0;; base += ER_CHUNK) {
-        const int niters = sh.niters;
-        if (base >= niters || sh.stop) break;
-        const int round = (n == 5) ? 1 : min(ER_CHUNK, niters - base);
-        // ---- sample (getSubset): draw until 5 distinct indices, draw order kept
-        if (tid == 0) {
-            for (int s = 0; s < round; s++) {
-                int* idx = sh.subsets[s];
-                if (n == 5) {  // count == modelPoints: the kernel runs once on all points
-                    for (int i = 0; i < 5; i++) idx[i] = i;
-                    continue;
-                }
-                for (int i = 0; i < 5; i++) {
-                    int v;
-                    bool dup;
-                    do {
-                        v = rng.uniform(0, n);
-                        dup = false;
-                        for (int k = 0; k < i; k++) dup |= idx[k] == v;
-                    } while (dup);
-                    idx[i] = v;
-                }
-            }
-        }
-        __syncthreads();
-        // ---- solve: one thread per iteration of the round.  The solver is a long serial fp64 chain (latency bound),
-        // so the 32 solves are spread over all 8 warps (4 lanes each): every SM sub-partition interleaves two
-        // independent instruction streams instead of idling behind one warp.
-        {
-            constexpr int LANES = ER_CHUNK / ER_WARPS;  // 4
-            if (lane < LANES) {
-                const int s = warp * LANES + lane;
-                int cnt = 0;
-                if (s < round) {
-                    double q1[5][2], q2[5][2];
-                    for (int i = 0; i < 5; i++) {
-                        const int k = sh.subsets[s][i];
-                        q1[i][0] = px1[k]; q1[i][1] = py1[k];
-                        q2[i][0] = px2[k]; q2[i][1] = py2[k];
-                    }
-                    cnt = cvm::five_point(q1, q2, models + (size_t)s * ER_MAXMODELS * 9);
-                }
-                sh.nmodels[s] = cnt;
-            }
-        }
-        __syncthreads();
-        if (warp == 0) {
-            // exclusive prefix of model counts -> flat hypothesis list
-            const int cnt = sh.nmodels[lane];
-            int incl = cnt;
+    // Durand-Kerner sweeps a solve may spend in the one-thread-per-iteration pass.  Converging polynomials need 15-45;
+    // about one in 4000 (a near-double root) never settles and OpenCV runs its full 300 sweeps on it — those are
+    // suspended and finished by a whole warp (cvm::dk_advance_warp) instead of stalling the round behind one thread.
+    static constexpr int DK_BUDGET = 48;
+    static constexpr bool HAS_TAIL = true;
+    struct Tail {
+        int slot, pad;
+        cvm::FPSetup fs;
+        cvm::DKState dk;
+    };
+    __device__ static int solve(const Params& prm, int p, const int* sub, double* models, int slot, Tail* tail,
+                                int* n_tail) {
+        const double* src = prm.pts + (size_t)p * 4 * prm.n_max;
+        double q1[5][2], q2[5][2];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            sh.hyp_offset[lane] = incl - cnt;
-            if (lane == 31) sh.hyp_offset[32] = incl;
+        for (int i = 0; i < 5; i++) {
+            const int k = sub[i];
+            q1[i][0] = src[k];
+            q1[i][1] = src[prm.n_max + k];
+            q2[i][0] = src[2 * prm.n_max + k];
+            q2[i][1] = src[3 * prm.n_max + k];
         }
-        __syncthreads();
-        // ---- score: one warp per hypothesis
-        const int H = sh.hyp_offset[ER_CHUNK];
-        for (int h = warp; h < H; h += ER_WARPS) {
-            // locate (s, k): largest s with hyp_offset[s] <= h  (32 entries, one per lane)
-            const unsigned le = __ballot_sync(0xffffffffu, sh.hyp_offset[lane] <= h && sh.nmodels[lane] > 0 &&
-                                                               h < sh.hyp_offset[lane] + sh.nmodels[lane]);
-            const int s = __ffs(le) - 1;
-            const int k = h - sh.hyp_offset[s];
-            double E[9];
-            const double* m = models + ((size_t)s * ER_MAXMODELS + k) * 9;
+        cvm::FPSetup fs;
+        if (!cvm::five_point_setup(q1, q2, fs)) return 0;
+        cvm::DKState dk;
+        cvm::dk_init(fs.coeffs, dk);
+        cvm::dk_advance(fs.coeffs, dk, DK_BUDGET);
+        if (!dk.done) {
+            const int t = atomicAdd(n_tail, 1);
+            if (t < rg::TAIL_CAP) {
+                tail[t].slot = slot;
+                tail[t].fs = fs;
+                tail[t].dk = dk;
+                return -1;
+            }
+            cvm::dk_advance(fs.coeffs, dk, 300);
+        }
+        cvm::Cplx roots[10];
+        const int n = cvm::dk_finish(dk, roots);
+        return cvm::five_point_models(fs, roots, n, models);
+    }
+    __device__ static int solve_tail(const Params&, Tail& T, double* models) {
+        cvm::DKState dk = T.dk;
+        double coeffs[11];
+#pragma unroll
+        for (int k = 0; k < 11; k++) coeffs[k] = T.fs.coeffs[k];
+        cvm::dk_advance_warp(coeffs, dk, 300);
+        int nm = 0;
+        if ((threadIdx.x & 31) == 0) {
+            cvm::Cplx roots[10];
+            const int n = cvm::dk_finish(dk, roots);
+            nm = cvm::five_point_models(T.fs, roots, n, models);
+        }
+        return nm;
+    }
+    struct Scorer {
+        double E[9];
+        __device__ Scorer(const Params&, const double* m) {
 #pragma unroll
             for (int i = 0; i < 9; i++) E[i] = m[i];
-            const int c = warp_count_inliers(E, px1, py1, px2, py2, n, thr2, lane);
-            if (lane == 0) sh.counts[s][k] = c;
         }
-        __syncthreads();
-        // ---- select: OpenCV's serial order over (iteration, candidate)
-        if (tid == 0) {
-            int nit = sh.niters, best = sh.best, done = sh.done_iters;
-            for (int s = 0; s < round; s++) {
-                const int it = base + s;
-                if (it >= nit) break;
-                for (int k = 0; k < sh.nmodels[s]; k++) {
-                    const int c = sh.counts[s][k];
-                    if (c > max(best, 4)) {
-                        best = c;
-                        const double* m = models + ((size_t)s * ER_MAXMODELS + k) * 9;
-                        for (int i = 0; i < 9; i++) sh.bestE[i] = m[i];
-                        nit = cvm::ransac_update_num_iters(prob, (double)(n - c) / n, 5, nit);
-                    }
-                }
-                done = it + 1;
-            }
-            sh.niters = nit;
-            sh.best = best;
-            sh.done_iters = done;
-            if (n == 5) sh.stop = 1;
+        __device__ bool inlier(const unsigned char* smem, const Params& prm, int i) const {
+            const double* s = reinterpret_cast<const double*>(smem);
+            return sampson_f32(E, s[i], s[prm.n_max + i], s[2 * prm.n_max + i], s[3 * prm.n_max + i]) <= prm.thr2;
         }
-        __syncthreads();
-    }
+    };
+};
 
-    // ---- outputs: the winner's mask is recomputed (identical arithmetic) instead of being stored per hypothesis
-    const int best = sh.best;
-    if (best == 0) {
-        for (int i = tid; i < n_max; i += ER_THREADS) mask[i] = 0;
-        if (tid < 9) Eo[tid] = 0.0;
-        if (tid == 0) {
-            n_inliers[p] = 0;
-            if (iters_run) iters_run[p] = sh.done_iters;
-            status[p] = FS_PAIR_NO_MODEL;
+__global__ void __launch_bounds__(256)
+k_er_normalise(const float* __restrict__ mkpts0, const float* __restrict__ mkpts1, const int32_t* __restrict__ n_corr,
+               int n_max, double focal, double ppx, double ppy, double* __restrict__ pts) {
+    const int p = blockIdx.y;
+    const int n = min(n_corr[p], n_max);
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float2 a = reinterpret_cast<const float2*>(mkpts0)[(size_t)p * n_max + i];
+    const float2 b = reinterpret_cast<const float2*>(mkpts1)[(size_t)p * n_max + i];
+    double* dst = pts + (size_t)p * 4 * n_max;
+    dst[i] = ((double)a.x - ppx) / focal;
+    dst[n_max + i] = ((double)a.y - ppy) / focal;
+    dst[2 * n_max + i] = ((double)b.x - ppx) / focal;
+    dst[3 * n_max + i] = ((double)b.y - ppy) / focal;
+}
+
+__global__ void __launch_bounds__(256)
+k_er_finish(const rg::PairState<9>* __restrict__ st, const double* __restrict__ pts, int n_max, float thr2,
+            double* __restrict__ E_out, uint8_t* __restrict__ mask_out, int32_t* __restrict__ n_inliers,
+            int32_t* __restrict__ iters_run, int32_t* __restrict__ status) {
+    const int p = blockIdx.y;
+    const rg::PairState<9>& S = st[p];
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool ok = S.status == FS_PAIR_OK;
+    if (blockIdx.x == 0) {
+        if (threadIdx.x < 9) E_out[9 * (size_t)p + threadIdx.x] = ok ? S.best_model[threadIdx.x] : 0.0;
+        if (threadIdx.x == 0) {
+            n_inliers[p] = ok ? (S.all_points ? 5 : S.best) : 0;
+            if (iters_run) iters_run[p] = S.status == FS_PAIR_TOO_FEW ? 0 : S.done;
+            status[p] = S.status;
         }
-        return;
     }
-    double E[9];
+    if (i >= n_max) return;
+    uint8_t v = 0;
+    if (ok && i < S.n) {
+        if (S.all_points) {
+            v = 1;
+        } else {
+            double E[9];
 #pragma unroll
-    for (int i = 0; i < 9; i++) E[i] = sh.bestE[i];
-    for (int i = tid; i < n_max; i += ER_THREADS) {
-        uint8_t v = 0;
-        if (i < n) v = (n == 5) ? 1 : (sampson_f32(E, px1[i], py1[i], px2[i], py2[i]) <= thr2 ? 1 : 0);
-        mask[i] = v;
+            for (int k = 0; k < 9; k++) E[k] = S.best_model[k];
+            const double* s = pts + (size_t)p * 4 * n_max;
+            v = sampson_f32(E, s[i], s[n_max + i], s[2 * n_max + i], s[3 * n_max + i]) <= thr2 ? 1 : 0;
+        }
     }
-    if (tid < 9) Eo[tid] = E[tid];
-    if (tid == 0) {
-        n_inliers[p] = (n == 5) ? 5 : best;
-        if (iters_run) iters_run[p] = sh.done_iters;
-        status[p] = FS_PAIR_OK;
-    }
+    mask_out[(size_t)p * n_max + i] = v;
 }
 
 __global__ void k_ransac_subsets(const int32_t* __restrict__ n_corr, int n_pairs, int max_iters,
@@ -297,37 +238,50 @@ k_score_essential(const float* __restrict__ mkpts0, const float* __restrict__ mk
     }
 }
 
-size_t er_smem_bytes(int n_max) {
-    return (size_t)n_max * 4 * sizeof(double) + (size_t)ER_CHUNK * ER_MAXMODELS * 9 * sizeof(double) +
-           sizeof(ERShared) + 64;
-}
-
 }  // namespace
 
-extern "C" size_t fs_find_essential_workspace_bytes(int, int, int) { return 256; }
+extern "C" size_t fs_find_essential_workspace_bytes(int n_pairs, int n_max, int max_iters) {
+    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    const size_t np = (size_t)(n_pairs > 0 ? n_pairs : 1), nm = (size_t)(n_max > 0 ? n_max : 1);
+    return fs::align_up(np * 4 * nm * sizeof(double), 256) + rg::Workspace<EPolicy>::bytes(n_pairs, pl) + 512;
+}
 
 extern "C" int fs_find_essential_ransac(const float* mkpts0, const float* mkpts1, const int32_t* n_corr, int n_pairs,
                                         int n_max, double focal, double pp_x, double pp_y, double prob,
                                         double threshold, int max_iters, double* E, uint8_t* mask,
-                                        int32_t* n_inliers, int32_t* iters_run, int32_t* status, void*, size_t,
-                                        fs_stream_t stream) {
+                                        int32_t* n_inliers, int32_t* iters_run, int32_t* status, void* workspace,
+                                        size_t workspace_bytes, fs_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
     FS_REQUIRE(n_pairs >= 0 && n_max >= 0, "negative size");
     if (n_pairs == 0) return FS_OK;
     FS_REQUIRE(n_max >= 1, "n_max must be positive");
+    FS_REQUIRE(n_pairs <= 65535, "n_pairs too large for one launch (limit 65535)");
     FS_REQUIRE(mkpts0 && mkpts1 && n_corr && E && mask && n_inliers && status, "null pointer");
     FS_REQUIRE(prob > 0 && prob < 1, "prob must be in (0, 1)");
     FS_REQUIRE(focal != 0, "focal must be non-zero");
-    const size_t smem = er_smem_bytes(n_max);
-    FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~6200)");
-    {
-        static int granted[64];
-        const int st_ = fs::ensure_dyn_smem(k_essential_ransac, granted, (size_t)((int)smem));
-        if (st_ != FS_OK) return st_;
+    const size_t smem = EPolicy::stage_bytes(n_max);
+    FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~7200)");
+    const size_t need = fs_find_essential_workspace_bytes(n_pairs, n_max, max_iters);
+    if (!workspace || workspace_bytes < need) {
+        fs::set_error("fs_find_essential_ransac: workspace %zu < %zu", workspace_bytes, need);
+        return FS_ERR_WORKSPACE;
     }
-    k_essential_ransac<<<n_pairs, ER_THREADS, smem, (cudaStream_t)stream>>>(
-        mkpts0, mkpts1, n_corr, n_max, focal, pp_x, pp_y, prob, threshold, max_iters, E, mask, n_inliers, iters_run,
-        status);
-    FS_LAUNCH_CHECK("k_essential_ransac");
+    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    FS_REQUIRE(pl.pool < (size_t)1 << 30, "n_pairs * max_iters too large");
+    fs::Carver cv(workspace);
+    double* pts = cv.take<double>((size_t)n_pairs * 4 * n_max);
+    rg::Workspace<EPolicy> ws;
+    ws.carve(cv, n_pairs, pl);
+    const double thr = threshold / ((focal + focal) / 2);
+    EPolicy::Params prm{pts, n_max, (float)(thr * thr)};
+    dim3 pgrid((n_max + 255) / 256, n_pairs);
+    k_er_normalise<<<pgrid, 256, 0, stream>>>(mkpts0, mkpts1, n_corr, n_max, focal, pp_x, pp_y, pts);
+    FS_LAUNCH_CHECK("k_er_normalise");
+    const int st_ = rg::run_rounds<EPolicy>(n_pairs, n_corr, n_max, /*min_points*/ 5, max_iters, prob, prm, pl, ws, smem,
+                                            stream);
+    if (st_ != FS_OK) return st_;
+    k_er_finish<<<pgrid, 256, 0, stream>>>(ws.st, pts, n_max, prm.thr2, E, mask, n_inliers, iters_run, status);
+    FS_LAUNCH_CHECK("k_er_finish");
     return FS_OK;
 }
 

@@ -214,11 +214,14 @@ int fs_score_pnp(const float* points3d, const float* pts2d, const int32_t* n_cor
  *     the reference) -> cheirality / distance (50) gates -> arg-max (first wins).
  * R [n_pairs, 9] f64, t [n_pairs, 3] f64 (unit norm), mask [n_pairs, n_max] u8 in {0,255},
  * n_good [n_pairs] i32.  Pairs whose status_in (may be NULL) is not FS_PAIR_OK are skipped (R = I, t = 0).
+ * workspace: fs_recover_pose_workspace_bytes(n_pairs) bytes (candidate poses + counters per pair).
  * ---------------------------------------------------------------------------------------------- */
+size_t fs_recover_pose_workspace_bytes(int n_pairs);
 int fs_recover_pose(const double* E, const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
                     const int32_t* status_in, int n_pairs, int n_max,
                     double focal, double pp_x, double pp_y, double distance_thresh,
-                    double* R, double* t, uint8_t* mask, int32_t* n_good, fs_stream_t stream);
+                    double* R, double* t, uint8_t* mask, int32_t* n_good,
+                    void* workspace, size_t workspace_bytes, fs_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
  * A7  PnP RANSAC — replaces
