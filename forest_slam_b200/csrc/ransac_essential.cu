@@ -47,6 +47,7 @@ struct EPolicy {
     static constexpr int MP = 5;     // model points
     static constexpr int MAXM = 10;  // candidate models per sample
     static constexpr int MD = 9;     // doubles per model
+    static constexpr int SLAB = 8;   // iterations scored by one CTA (<= 80 hypotheses)
     struct Params {
         const double* pts;  // [n_pairs][4][n_max]: x1 | y1 | x2 | y2, normalised
         int n_max;

@@ -15,7 +15,7 @@
 //   solve  : one THREAD per slot, slots dealt round-robin over one warp per SM sub-partition so that every warp carries
 //            as few latency-bound solves as possible; a policy may suspend a rare long-running solve and hand it to
 //   tail   : one WARP per suspended solve (warp-cooperative continuation, same arithmetic).
-//   score  : one CTA per slab of SLAB consecutive slots of one pair: the pair's correspondences are staged in shared
+//   score  : one CTA per slab of Pol::SLAB consecutive slots of one pair: the pair's correspondences are staged in shared
 //            memory once, then ONE WARP PER HYPOTHESIS counts inliers (ballot-free: per-lane count + redux).
 // The first round speculates FIRST_CHUNK iterations per pair; later rounds share the pool between the pairs still
 // running (a straggler that needs hundreds of iterations gets them in one round).  The number of rounds launched is
@@ -31,7 +31,6 @@
 namespace rg {
 
 constexpr int FIRST_CHUNK = 64;   // speculative iterations per pair in round 0
-constexpr int SLAB = 8;           // slots scored by one CTA (slot ranges of a pair are SLAB-aligned)
 constexpr int SCORE_THREADS = 256;
 constexpr int SOLVE_THREADS = 64;
 constexpr int SELECT_THREADS = 256;
@@ -133,8 +132,8 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
         nit = max(max_iters, 1);
         best = 0;
         done = 0;
-        allp = (n == MP);
         active = n >= max(min_points, MP);
+        allp = active && n == MP;
         rng_state = 0xFFFFFFFFFFFFFFFFull;  // RNG rng((uint64)-1) inside run()
         if (lane == 0) {
             S.n = n;
@@ -195,10 +194,10 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
             chunk = min(FIRST_CHUNK, nit);
         } else {
             const int prev_active = max(ws.ctl[round - 1].n_active, 1);
-            const int share = max((pool / prev_active) & ~(SLAB - 1), SLAB);
+            const int share = max((pool / prev_active) & ~(Pol::SLAB - 1), Pol::SLAB);
             chunk = min(nit - done, share);
         }
-        const int alloc = (chunk + SLAB - 1) / SLAB * SLAB;
+        const int alloc = (chunk + Pol::SLAB - 1) / Pol::SLAB * Pol::SLAB;
         if (lane == 0) {
             slot_base = atomicAdd(&ws.ctl[round].n_used, alloc);
             atomicAdd(&ws.ctl[round].n_active, 1);
@@ -287,9 +286,9 @@ template <class Pol>
 __global__ void __launch_bounds__(SCORE_THREADS)
 k_rg_score(int round, typename Pol::Params prm, Workspace<Pol> ws) {
     extern __shared__ __align__(16) unsigned char rg_smem[];
-    __shared__ int s_off[SLAB + 1];
+    __shared__ int s_off[Pol::SLAB + 1];
     const int used = ws.ctl[round].n_used;
-    const int slab0 = blockIdx.x * SLAB;
+    const int slab0 = blockIdx.x * Pol::SLAB;
     if (slab0 >= used) return;
     const int p = ws.slot_pair[slab0];
     if (p < 0) return;
@@ -297,19 +296,19 @@ k_rg_score(int round, typename Pol::Params prm, Workspace<Pol> ws) {
     Pol::stage(prm, p, n, rg_smem);
     if (threadIdx.x == 0) {
         int o = 0;
-        for (int s = 0; s < SLAB; s++) {
+        for (int s = 0; s < Pol::SLAB; s++) {
             s_off[s] = o;
             o += (ws.slot_pair[slab0 + s] == p) ? ws.slot_nmodels[slab0 + s] : 0;
         }
-        s_off[SLAB] = o;
+        s_off[Pol::SLAB] = o;
     }
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int H = s_off[SLAB];
+    const int H = s_off[Pol::SLAB];
     for (int h = warp; h < H; h += SCORE_THREADS / 32) {
         int s = 0;
 #pragma unroll
-        for (int j = 1; j < SLAB; j++) s += (s_off[j] <= h) ? 1 : 0;
+        for (int j = 1; j < Pol::SLAB; j++) s += (s_off[j] <= h) ? 1 : 0;
         const int k = h - s_off[s];
         const int slot = slab0 + s;
         typename Pol::Scorer sc(prm, ws.slot_models + ((size_t)slot * Pol::MAXM + k) * Pol::MD);
@@ -338,7 +337,7 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
     solve_warps = min(solve_warps, fs::sm_count() * 4);  // measured: beyond one solver warp per SM sub-partition the
                                                          // fp64 issue slots are shared and every solve gets slower
     const int solve_grid = (solve_warps + SOLVE_THREADS / 32 - 1) / (SOLVE_THREADS / 32);
-    const int score_grid = (pool + SLAB - 1) / SLAB;
+    const int score_grid = (pool + Pol::SLAB - 1) / Pol::SLAB;
     for (int r = 0; r <= pl.rounds; r++) {
         k_rg_select<Pol><<<sel_grid, SELECT_THREADS, 0, stream>>>(r, n_pairs, n_corr, n_max, min_points, max_iters,
                                                                   confidence, pool, ws);
@@ -351,7 +350,7 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
             FS_LAUNCH_CHECK("k_rg_tail");
         }
         // round 0 uses FIRST_CHUNK slots per pair at most
-        const int sg = (r == 0) ? min(score_grid, (n_pairs * FIRST_CHUNK + SLAB - 1) / SLAB) : score_grid;
+        const int sg = (r == 0) ? min(score_grid, (n_pairs * FIRST_CHUNK + Pol::SLAB - 1) / Pol::SLAB) : score_grid;
         k_rg_score<Pol><<<sg, SCORE_THREADS, stage_smem, stream>>>(r, prm, ws);
         FS_LAUNCH_CHECK("k_rg_score");
     }

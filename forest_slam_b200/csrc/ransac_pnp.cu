@@ -3,6 +3,7 @@
 // with the reference's distortion coefficients in OpenCV's operation order, float32 error <= (float)thr^2.
 #include "common.cuh"
 #include "epnp.cuh"
+#include "ransac_grid.cuh"
 
 namespace {
 
@@ -82,178 +83,147 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
 
 
 // ------------------------------------------------------------------------------------------------ A7 RANSAC
-// One CTA per frame pair, rounds of PR_CHUNK RANSAC iterations (same structure as k_essential_ransac):
-//   sample : thread 0 replays cv::RNG(2^64-1) (RANSACPointSetRegistrator::getSubset);
-//   solve  : PR_CHUNK threads spread over all warps, one EPnP-on-5-points each (epnp.cuh) -> model (rvec | tvec) in
-//            shared memory;
-//   score  : ONE WARP PER HYPOTHESIS over all correspondences staged in shared memory: projectPoints with the
-//            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, ballot/popc count;
-//   select : thread 0 walks the counts in OpenCV's serial order (strictly greater, adaptive iteration cap).
-constexpr int PR_THREADS = 256;
-constexpr int PR_WARPS = PR_THREADS / 32;
-constexpr int PR_CHUNK = 128;  // speculative iterations per round: the EPnP solves are latency bound, so a round of 128
-                               // (16 lanes x 8 warps) costs about as much as a round of 32 and cuts the number of rounds by 4
-
-struct PRShared {
-    double models[PR_CHUNK][6];
-    int counts[PR_CHUNK];
-    int subsets[PR_CHUNK][5];
-    int niters, best, done_iters;
-    double best_model[6];
+// Runs on the batch-wide engine of ransac_grid.cuh (rounds of select + sample / solve / score over the whole GPU):
+//   solve  : one thread per RANSAC iteration, EPnP-on-5-points (epnp.cuh) -> one model (rvec | tvec);
+//   score  : ONE WARP PER HYPOTHESIS over the pair's correspondences staged in shared memory: projectPoints with the
+//            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, warp-reduced count;
+//   finish : mask of the winner (identical arithmetic) + ascending inlier index list.
+struct PPolicy {
+    static constexpr int MP = 5;
+    static constexpr int MAXM = 1;
+    static constexpr int MD = 6;
+    static constexpr int SLAB = 32;  // iterations (= hypotheses) scored by one CTA
+    static constexpr bool HAS_TAIL = false;
+    struct Tail {
+        int slot;
+    };
+    struct Params {
+        const float* points3d;  // [n_pairs][n_max][3]
+        const float* pts2d;     // [n_pairs][n_max][2]
+        int n_max;
+        float thr2;
+        cvm::CamD cam;
+    };
+    static size_t stage_bytes(int n_max) { return PnPStage::bytes(n_max); }
+    __device__ static void stage(const Params& prm, int p, int n, unsigned char* smem) {
+        PnPStage st;
+        st.carve(smem, prm.n_max);
+        st.load(prm.points3d + 3 * (size_t)p * prm.n_max, prm.pts2d + 2 * (size_t)p * prm.n_max, n);
+    }
+    __device__ static int solve(const Params& prm, int p, const int* sub, double* model, int, Tail*, int*) {
+        const float* p3 = prm.points3d + 3 * (size_t)p * prm.n_max;
+        const float2* p2 = reinterpret_cast<const float2*>(prm.pts2d) + (size_t)p * prm.n_max;
+        double obj[5][3];
+        float img[5][2];
+#pragma unroll
+        for (int i = 0; i < 5; i++) {
+            const int k = sub[i];
+            obj[i][0] = (double)p3[3 * k];
+            obj[i][1] = (double)p3[3 * k + 1];
+            obj[i][2] = (double)p3[3 * k + 2];
+            const float2 q = p2[k];
+            img[i][0] = q.x;
+            img[i][1] = q.y;
+        }
+        double m[6];
+        cvm::pnp_minimal_epnp5(prm.cam, obj, img, m);
+#pragma unroll
+        for (int i = 0; i < 6; i++) model[i] = m[i];
+        return 1;
+    }
+    __device__ static int solve_tail(const Params&, Tail&, double*) { return 0; }
+    struct Scorer {
+        double R[9], t[3];
+        __device__ Scorer(const Params&, const double* m) {
+            double rv[3];
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+                rv[i] = m[i];
+                t[i] = m[3 + i];
+            }
+            cvm::rodrigues_vec2mat(rv, R);
+        }
+        __device__ bool inlier(unsigned char* smem, const Params& prm, int i) const {
+            PnPStage st;
+            st.carve(smem, prm.n_max);
+            float pu, pv;
+            cvm::project_point_f32(R, t, prm.cam, st.X[i], st.Y[i], st.Z[i], pu, pv);
+            return cvm::reproj_err_f32(st.u[i], st.v[i], pu, pv) <= prm.thr2;
+        }
+    };
 };
 
-__global__ void __launch_bounds__(PR_THREADS)
-k_pnp_ransac(const float* __restrict__ points3d, const float* __restrict__ pts2d, const int32_t* __restrict__ n_corr,
-             int n_max, FSCamera cam_, double reproj_error, double confidence, int max_iters, int min_points,
-             double* __restrict__ model_out, uint8_t* __restrict__ mask_out, int32_t* __restrict__ inlier_idx,
-             int32_t* __restrict__ n_inliers, int32_t* __restrict__ iters_run, int32_t* __restrict__ status) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    PnPStage st;
-    st.carve(smem_raw, n_max);
-    PRShared& sh = *reinterpret_cast<PRShared*>(smem_raw + (PnPStage::bytes(n_max) + 15) / 16 * 16);
-    __shared__ int s_warp[33];
+// rare path (exactly 5 correspondences) kept out of line so that it does not set the register budget of k_pnp_finish
+__device__ __noinline__ void epnp5_all_points(const cvm::CamD& cam, const float* p3, const float2* p2, double* m) {
+    double obj[5][3];
+    float img[5][2];
+    for (int i = 0; i < 5; i++) {
+        obj[i][0] = (double)p3[3 * i]; obj[i][1] = (double)p3[3 * i + 1]; obj[i][2] = (double)p3[3 * i + 2];
+        img[i][0] = p2[i].x; img[i][1] = p2[i].y;
+    }
+    cvm::pnp_minimal_epnp5(cam, obj, img, m);
+}
 
+constexpr int PF_THREADS = 256;
+constexpr int PF_WARPS = PF_THREADS / 32;
+
+// one CTA per pair: outputs of the RANSAC stage (model, {0,1} mask, ascending inlier list, status)
+__global__ void __launch_bounds__(PF_THREADS)
+k_pnp_finish(const rg::PairState<6>* __restrict__ stt, PPolicy::Params prm, double* __restrict__ model_out,
+             uint8_t* __restrict__ mask_out, int32_t* __restrict__ inlier_idx, int32_t* __restrict__ n_inliers,
+             int32_t* __restrict__ iters_run, int32_t* __restrict__ status) {
+    __shared__ int s_warp[33];
+    __shared__ double s_model[6];
     const int p = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = min(n_corr[p], n_max);
+    const rg::PairState<6>& S = stt[p];
+    const int n_max = prm.n_max, n = S.n;
     uint8_t* mask = mask_out + (size_t)p * n_max;
     double* mo = model_out + 6 * (size_t)p;
-    const cvm::CamD cam = to_cam(cam_);
-
-    if (n < max(min_points, 5)) {  // stereo_slam.py:292 gate (6); below 5 OpenCV switches to P3P (not on the path)
-        for (int i = tid; i < n_max; i += PR_THREADS) mask[i] = 0;
-        if (tid < 6) mo[tid] = 0.0;
-        if (tid == 0) {
-            n_inliers[p] = 0;
-            if (iters_run) iters_run[p] = 0;
-            status[p] = FS_PAIR_TOO_FEW;
-        }
-        return;
-    }
-    st.load(points3d + 3 * (size_t)p * n_max, pts2d + 2 * (size_t)p * n_max, n);
-    const float thr2 = (float)(reproj_error * reproj_error);
-    cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
-    if (tid == 0) {
-        sh.niters = max(max_iters, 1);
-        sh.best = 0;
-        sh.done_iters = 0;
-    }
-    __syncthreads();
-
-    if (n == 5) {
+    const float* p3 = prm.points3d + 3 * (size_t)p * n_max;
+    const float2* p2 = reinterpret_cast<const float2*>(prm.pts2d) + (size_t)p * n_max;
+    if (S.all_points) {
         // model_points == npoints: solvePnP(EPNP) on all points, every point an inlier, no refit
         if (tid == 0) {
-            double obj[5][3];
-            float img[5][2];
-            for (int i = 0; i < 5; i++) {
-                obj[i][0] = st.X[i]; obj[i][1] = st.Y[i]; obj[i][2] = st.Z[i];
-                img[i][0] = st.u[i]; img[i][1] = st.v[i];
-            }
             double m[6];
-            cvm::pnp_minimal_epnp5(cam, obj, img, m);
+            epnp5_all_points(prm.cam, p3, p2, m);
             for (int i = 0; i < 6; i++) mo[i] = m[i];
             n_inliers[p] = 5;
             if (iters_run) iters_run[p] = 0;
             status[p] = FS_PAIR_OK;
         }
-        for (int i = tid; i < n_max; i += PR_THREADS) {
+        for (int i = tid; i < n_max; i += PF_THREADS) {
             mask[i] = i < 5 ? 1 : 0;
             if (inlier_idx && i < 5) inlier_idx[(size_t)p * n_max + i] = i;
         }
         return;
     }
-
-    for (int base = 0;; base += PR_CHUNK) {
-        const int niters = sh.niters;
-        if (base >= niters) break;
-        const int round = min(PR_CHUNK, niters - base);
-        if (tid == 0) {
-            for (int s = 0; s < round; s++) {
-                int* idx = sh.subsets[s];
-                for (int i = 0; i < 5; i++) {
-                    int v;
-                    bool dup;
-                    do {
-                        v = rng.uniform(0, n);
-                        dup = false;
-                        for (int k = 0; k < i; k++) dup |= idx[k] == v;
-                    } while (dup);
-                    idx[i] = v;
-                }
-            }
-        }
-        __syncthreads();
-        // the minimal solver is a long serial fp64 chain: spread the 32 solves over all 8 warps (4 lanes each)
-        const int sidx = warp * (PR_CHUNK / PR_WARPS) + lane;
-        if (lane < PR_CHUNK / PR_WARPS && sidx < round) {
-            double obj[5][3];
-            float img[5][2];
-            for (int i = 0; i < 5; i++) {
-                const int k = sh.subsets[sidx][i];
-                obj[i][0] = st.X[k]; obj[i][1] = st.Y[k]; obj[i][2] = st.Z[k];
-                img[i][0] = st.u[k]; img[i][1] = st.v[k];
-            }
-            double m[6];
-            cvm::pnp_minimal_epnp5(cam, obj, img, m);
-            for (int i = 0; i < 6; i++) sh.models[sidx][i] = m[i];
-        }
-        __syncthreads();
-        for (int h = warp; h < round; h += PR_WARPS) {
-            double rv[3], t[3], R[9];
-            for (int i = 0; i < 3; i++) {
-                rv[i] = sh.models[h][i];
-                t[i] = sh.models[h][3 + i];
-            }
-            cvm::rodrigues_vec2mat(rv, R);
-            const int c = warp_count_reproj(R, t, cam, st, n, thr2, lane);
-            if (lane == 0) sh.counts[h] = c;
-        }
-        __syncthreads();
-        if (tid == 0) {
-            int nit = sh.niters, best = sh.best, done = sh.done_iters;
-            for (int s = 0; s < round; s++) {
-                const int it = base + s;
-                if (it >= nit) break;
-                const int c = sh.counts[s];
-                if (c > max(best, 4)) {
-                    best = c;
-                    for (int i = 0; i < 6; i++) sh.best_model[i] = sh.models[s][i];
-                    nit = cvm::ransac_update_num_iters(confidence, (double)(n - c) / n, 5, nit);
-                }
-                done = it + 1;
-            }
-            sh.niters = nit;
-            sh.best = best;
-            sh.done_iters = done;
-        }
-        __syncthreads();
-    }
-
-    const int best = sh.best;
-    if (best == 0) {
-        for (int i = tid; i < n_max; i += PR_THREADS) mask[i] = 0;
+    if (S.status != FS_PAIR_OK) {
+        for (int i = tid; i < n_max; i += PF_THREADS) mask[i] = 0;
         if (tid < 6) mo[tid] = 0.0;
         if (tid == 0) {
             n_inliers[p] = 0;
-            if (iters_run) iters_run[p] = sh.done_iters;
-            status[p] = FS_PAIR_NO_MODEL;
+            if (iters_run) iters_run[p] = S.status == FS_PAIR_TOO_FEW ? 0 : S.done;
+            status[p] = S.status;
         }
         return;
     }
+    if (tid < 6) s_model[tid] = S.best_model[tid];
+    __syncthreads();
     double rv[3], t[3], R[9];
     for (int i = 0; i < 3; i++) {
-        rv[i] = sh.best_model[i];
-        t[i] = sh.best_model[3 + i];
+        rv[i] = s_model[i];
+        t[i] = s_model[3 + i];
     }
     cvm::rodrigues_vec2mat(rv, R);
-    // mask of the winner (identical arithmetic to the scoring pass) + ascending inlier index list
     int basei = 0;
-    for (int i0 = 0; i0 < n_max; i0 += PR_THREADS) {
+    for (int i0 = 0; i0 < n_max; i0 += PF_THREADS) {
         const int i = i0 + tid;
         bool in = false;
         if (i < n) {
             float pu, pv;
-            cvm::project_point_f32(R, t, cam, st.X[i], st.Y[i], st.Z[i], pu, pv);
-            in = cvm::reproj_err_f32(st.u[i], st.v[i], pu, pv) <= thr2;
+            cvm::project_point_f32(R, t, prm.cam, (double)p3[3 * i], (double)p3[3 * i + 1], (double)p3[3 * i + 2], pu, pv);
+            const float2 q = p2[i];
+            in = cvm::reproj_err_f32(q.x, q.y, pu, pv) <= prm.thr2;
         }
         if (i < n_max) mask[i] = in ? 1 : 0;
         const unsigned bal = __ballot_sync(0xffffffffu, in);
@@ -261,7 +231,7 @@ k_pnp_ransac(const float* __restrict__ points3d, const float* __restrict__ pts2d
         if (lane == 0) s_warp[warp] = __popc(bal);
         __syncthreads();
         if (warp == 0) {
-            int v = lane < PR_WARPS ? s_warp[lane] : 0, incl = v;
+            int v = lane < PF_WARPS ? s_warp[lane] : 0, incl = v;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const int nb = __shfl_up_sync(0xffffffffu, incl, o);
@@ -275,10 +245,10 @@ k_pnp_ransac(const float* __restrict__ points3d, const float* __restrict__ pts2d
             inlier_idx[(size_t)p * n_max + basei + s_warp[warp] + __popc(bal & ((1u << lane) - 1))] = i;
         basei += s_warp[32];
     }
-    if (tid < 6) mo[tid] = sh.best_model[tid];
+    if (tid < 6) mo[tid] = s_model[tid];
     if (tid == 0) {
-        n_inliers[p] = best;
-        if (iters_run) iters_run[p] = sh.done_iters;
+        n_inliers[p] = S.best;
+        if (iters_run) iters_run[p] = S.done;
         status[p] = FS_PAIR_OK;
     }
 }
@@ -515,8 +485,10 @@ extern "C" int fs_score_pnp(const float* points3d, const float* pts2d, const int
 }
 
 
-extern "C" size_t fs_solve_pnp_workspace_bytes(int n_pairs, int, int) {
-    return fs::align_up((size_t)(n_pairs > 0 ? n_pairs : 1) * 6 * sizeof(double), 256) + 256;
+extern "C" size_t fs_solve_pnp_workspace_bytes(int n_pairs, int, int max_iters) {
+    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    return fs::align_up((size_t)(n_pairs > 0 ? n_pairs : 1) * 6 * sizeof(double), 256) +
+           rg::Workspace<PPolicy>::bytes(n_pairs, pl) + 512;
 }
 
 extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, const int32_t* n_corr, int n_pairs,
@@ -530,24 +502,31 @@ extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, co
     FS_REQUIRE(n_max >= 1, "n_max must be positive");
     FS_REQUIRE(points3d && pts2d && n_corr && cam && rvec && tvec && mask && n_inliers && status, "null pointer");
     FS_REQUIRE(confidence > 0 && confidence < 1, "confidence must be in (0, 1)");
-    if (!workspace || workspace_bytes < fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters)) {
-        fs::set_error("fs_solve_pnp_ransac: workspace %zu < %zu", workspace_bytes,
-                      fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters));
+    const size_t need = fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters);
+    if (!workspace || workspace_bytes < need) {
+        fs::set_error("fs_solve_pnp_ransac: workspace %zu < %zu", workspace_bytes, need);
         return FS_ERR_WORKSPACE;
     }
-    fs::Carver ws(workspace);
-    double* model = ws.take<double>((size_t)n_pairs * 6);
-    const size_t smem = fs::align_up(PnPStage::bytes(n_max), 16) + sizeof(PRShared) + 16;
-    FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~7000)");
-    {
-        static int granted[64];
-        const int st_ = fs::ensure_dyn_smem(k_pnp_ransac, granted, (size_t)((int)smem));
-        if (st_ != FS_OK) return st_;
-    }
-    k_pnp_ransac<<<n_pairs, PR_THREADS, smem, stream>>>(points3d, pts2d, n_corr, n_max, *cam, reproj_error, confidence,
-                                                       max_iters, min_points, model, mask, inlier_idx, n_inliers,
-                                                       iters_run, status);
-    FS_LAUNCH_CHECK("k_pnp_ransac");
+    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    FS_REQUIRE(pl.pool < (size_t)1 << 30, "n_pairs * max_iters too large");
+    fs::Carver cv(workspace);
+    double* model = cv.take<double>((size_t)n_pairs * 6);
+    rg::Workspace<PPolicy> ws;
+    ws.carve(cv, n_pairs, pl);
+    const size_t smem = PPolicy::stage_bytes(n_max);
+    FS_REQUIRE(smem <= 227 * 1024, "n_max too large for the shared-memory staging (limit ~7200)");
+    PPolicy::Params prm;
+    prm.points3d = points3d;
+    prm.pts2d = pts2d;
+    prm.n_max = n_max;
+    prm.thr2 = (float)(reproj_error * reproj_error);
+    prm.cam.fx = cam->fx; prm.cam.fy = cam->fy; prm.cam.cx = cam->cx; prm.cam.cy = cam->cy;
+    for (int i = 0; i < 5; i++) prm.cam.k[i] = cam->dist[i];
+    const int st_ = rg::run_rounds<PPolicy>(n_pairs, n_corr, n_max, min_points, max_iters, confidence, prm, pl, ws, smem,
+                                            stream);
+    if (st_ != FS_OK) return st_;
+    k_pnp_finish<<<n_pairs, PF_THREADS, 0, stream>>>(ws.st, prm, model, mask, inlier_idx, n_inliers, iters_run, status);
+    FS_LAUNCH_CHECK("k_pnp_finish");
     k_pnp_refine<<<n_pairs, RF_THREADS, 0, stream>>>(points3d, pts2d, n_corr, n_max, *cam, model, mask, n_inliers,
                                                     status, rvec, tvec);
     FS_LAUNCH_CHECK("k_pnp_refine");
