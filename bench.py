@@ -40,11 +40,13 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="mono", choices=["mono", "stereo"])
-    ap.add_argument("--pairs", type=int, default=128, help="frame pairs per step per GPU")
+    ap.add_argument("--pairs", type=int, default=256, help="frame pairs per step per GPU")
     ap.add_argument("--kpts", type=int, default=0, help="keypoints per frame (default 2048 mono / 2000 stereo)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="pairs timed for cpu_baseline (0 = auto)")
     ap.add_argument("--exact-fp32", action="store_true", help="CUDA-core fp32 matcher instead of tcgen05")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--overlap-steps", type=int, default=1,
+                    help="1: consecutive steps alternate between two streams (software pipelining across steps)")
     ap.add_argument("--pos-outlier", type=float, default=-1.0,
                     help="probability that an observation is a gross positional outlier (default 0.1 mono, 0 stereo)")
     return ap.parse_args()
@@ -215,6 +217,34 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------ B200 arm
+# stage of the step -> the kernel that is (all but a few microseconds of) it; ncu launch lists under profiles/ use
+# these names
+STAGE_KERNEL = {"match": {"mono": "k_float_match_tc", "stereo": "k_hamming_top2"}, "prepare": "k_float_prepare",
+                "gather": "k_gather_matches", "essential_ransac": "k_rg_select/solve/tail/score<EPolicy> rounds",
+                "recover_pose": "k_rp_cheirality", "triangulate": "k_backproject_filter",
+                "pnp_ransac": "k_rg_select/solve/score<PPolicy> rounds + k_pnp_refine"}
+
+
+def kernel_of(stage: str, workload: str) -> str:
+    k = STAGE_KERNEL.get(stage, stage)
+    return k[workload] if isinstance(k, dict) else k
+
+
+def measured_traffic(kernel: str, args, wl):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of the same
+    command (profiles/traffic.json: kernel -> {"pairs": P, "kpts": n, "bytes": B}); None when no capture matches."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    if not os.path.exists(path):
+        return None
+    try:
+        t = json.load(open(path)).get(kernel)
+    except Exception:
+        return None
+    if not t or t.get("pairs") != args.pairs or t.get("kpts") != wl["n_kpts"]:
+        return None
+    return t.get("bytes")
+
+
 def stage_work(args, wl, res, stage: str):
     """Algorithmic work of one step of `stage` (SURVEY §8d figures): (bound, amount, unit)."""
     P, n = args.pairs, wl["n_kpts"]
@@ -222,6 +252,8 @@ def stage_work(args, wl, res, stage: str):
     it = float(res["iters"].float().mean().item()) if "iters" in res else 0.0
     if stage == "match" and args.workload == "mono":
         return "tensor", P * 2.0 * n * n * 256, "TFLOP/s"
+    if stage == "prepare":
+        return "hbm", (P + 1) * n * 256 * (4.0 + 4.0), "GB/s"  # fp32 in, fp16 hi + lo out, once per frame
     if stage == "match":
         return "hbm", P * ((n + n) * 32.0 + n * 12.0), "GB/s"
     if stage == "essential_ransac":
@@ -308,37 +340,51 @@ def run_b200(args):
     kw = (dict(descriptor="float", scale=0.0625, threshold=LN_THRESH, exact_fp32=args.exact_fp32)
           if args.workload == "mono" else dict(descriptor="binary"))
     pipe = seq.CapturedPipeline(bank, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw)
-    for _ in range(max(args.warmup, 3)):
-        pipe.run()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    # second pipeline on its own input buffers: consecutive steps alternate between the two, each on its own stream,
+    # so that the latency-bound RANSAC rounds of step i run beside the tensor-core matcher of step i+1 (this is how a
+    # streaming caller drives the path; the e2e loop below uses the same pair of pipelines with uploads in between)
+    devbuf2 = {k: v.clone() for k, v in devbuf.items()}
+    bank2 = seq.FrameBank(kpts=devbuf2["kpts"], counts=devbuf2["counts"], desc_f32=devbuf2.get("desc_f32"),
+                          desc_bin=devbuf2.get("desc_bin"), disparity=devbuf2.get("disparity"))
+    pipe2 = seq.CapturedPipeline(bank2, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw)
+    pipes, bufs = [pipe, pipe2], [devbuf, devbuf2]
+    main = torch.cuda.current_stream(dev)
+    lanes = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)] if args.overlap_steps else [main, main]
+    flushes = [flush, torch.empty_like(flush)] if args.overlap_steps else [flush, flush]
+
+    def device_loop(n_steps):
+        """n_steps steps with the frame bank resident in HBM; returns (results, records) of the last step."""
+        out = None
+        for st_ in lanes:
+            st_.wait_stream(main)
+        for i in range(n_steps):
+            with torch.cuda.stream(lanes[i & 1]):
+                flushes[i & 1].zero_()  # L2 flush before every step (a 256 MB write, > 126 MB L2)
+                out = pipes[i & 1].run()
+        for st_ in lanes:
+            main.wait_stream(st_)
+        return out
+
+    device_loop(max(args.warmup, 3))
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
     wall0 = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()  # L2 flush between timed iterations (outside the per-step events)
-        ev[i][0].record()
-        res, allrec = pipe.run()
-        ev[i][1].record()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    res, allrec = device_loop(args.steps)
+    e1.record()
     barrier()
     wall = time.perf_counter() - wall0
     clk = clocks.stop()
     launches = launches_per_step * args.steps
-    t_dev = sum(a.elapsed_time(b) for a, b in ev) / 1e3
+    t_dev = e0.elapsed_time(e1) / 1e3
     # ---- end-to-end through the public API with host buffers.  Every step copies ITS frame bank from pinned host
     # memory into the pipeline's input tensors, replays the step and reads the gathered records back to the host —
     # all inside the timed region.  Two pipelines (A/B input buffers) alternate so that the upload of step i+1 runs on
     # a copy stream while step i computes; the per-step L2 flush stays on the compute stream.
-    devbuf2 = {k: torch.empty_like(v) for k, v in devbuf.items()}
-    bank2 = seq.FrameBank(kpts=devbuf2["kpts"], counts=devbuf2["counts"], desc_f32=devbuf2.get("desc_f32"),
-                          desc_bin=devbuf2.get("desc_bin"), disparity=devbuf2.get("disparity"))
-    for k, v in host.items():
-        devbuf2[k].copy_(v)
-    pipe2 = seq.CapturedPipeline(bank2, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw)
-    pipes, bufs = [pipe, pipe2], [devbuf, devbuf2]
     rec_hosts = [rec_host, torch.empty_like(rec_host).pin_memory()]
     copy_stream = torch.cuda.Stream(device=dev)
-    main = torch.cuda.current_stream(dev)
 
     def e2e_loop(n_steps):
         copied = [torch.cuda.Event() for _ in range(2)]
@@ -408,8 +454,10 @@ def run_b200(args):
             "e2e": {"value": total_pairs / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d_bytes),
                     "d2h_bytes_per_step": int(rec_host.numel() * 8)},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": dom, "bound": bound, "achieved": achieved, "peak": peak, "unit": unit,
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "roofline": {"kernel": kernel_of(dom, args.workload), "stage": dom, "bound": bound, "achieved": achieved,
+                         "peak": peak, "unit": unit, "frac": achieved / peak,
+                         "traffic": measured_traffic(kernel_of(dom, args.workload), args, wl),
+                         "peak_source": peak_src,
                          "stage_ms_per_step": {k: v / args.steps for k, v in stages.items()}},
             "wall_s": wall,
             "stats": {"mean_matches": float(res["n_matches"].float().mean()),

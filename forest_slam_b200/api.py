@@ -88,10 +88,28 @@ def _stream():
 
 
 _workspaces = {}
+_ws_scope = ["global"]
+
+
+class workspace_scope:
+    """Private workspace set for everything enqueued inside the `with` block.  Workspaces are cached per
+    (device, operator); two launch sequences that may run CONCURRENTLY (two captured pipelines replayed on two
+    streams) must not share them, so each captures under its own scope."""
+
+    def __init__(self, name: str):
+        self.name = name
+
+    def __enter__(self):
+        _ws_scope.append(self.name)
+        return self
+
+    def __exit__(self, *exc):
+        _ws_scope.pop()
+        return False
 
 
 def _workspace(nbytes: int, device: torch.device, slot: str = "default") -> torch.Tensor:
-    key = (device.index, slot)
+    key = (device.index, slot, _ws_scope[-1])
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=device)

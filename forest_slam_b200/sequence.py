@@ -68,17 +68,24 @@ def _run(timer, name, fn):
     return fn() if timer is None else timer.run(name, fn)
 
 
-def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp32: bool, scale: float = 1.0):
+def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp32: bool, scale: float = 1.0,
+           timer=None):
     if descriptor == "float":
         if bank.desc_f32 is None and bank.operands is None:
             raise ValueError("the frame bank holds no float descriptors")
-        r = api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale, threshold=threshold, ratio=ratio,
-                                  operands=bank.operands, exact_fp32=exact_fp32)
+        operands = bank.operands
+        n_max = int(bank.desc_f32.shape[2]) if bank.desc_f32 is not None else int(bank.operands.shape[1])
+        if operands is None and not exact_fp32 and api.TENSOR_CORE_MATCHER and n_max % 128 == 0:
+            # fp32 channel-major descriptors -> split-fp16 operand rows, once per frame (not per pair)
+            operands = _run(timer, "prepare", lambda: api.float_prepare(bank.desc_f32, bank.counts))
+        r = _run(timer, "match", lambda: api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale,
+                                                               threshold=threshold, ratio=ratio, operands=operands,
+                                                               exact_fp32=exact_fp32))
     elif descriptor == "binary":
         if bank.desc_bin is None:
             raise ValueError("the frame bank holds no binary descriptors")
-        r = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, ratio=ratio,
-                                    want_matches1=False)
+        r = _run(timer, "match", lambda: api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True,
+                                                                 ratio=ratio, want_matches1=False))
     else:
         raise ValueError("descriptor must be 'float' or 'binary'")
     return r
@@ -93,7 +100,7 @@ def mono_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "float", ca
     dev = bank.kpts.device
     pa = api._to_cuda(pair_a, torch.int32, dev)
     pb = api._to_cuda(pair_b, torch.int32, dev)
-    m = _run(timer, "match", lambda: _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale))
+    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer)
     g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
     pp = (camera.cx, camera.cy)
     e = _run(timer, "essential_ransac",
@@ -118,7 +125,7 @@ def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary",
     dev = bank.kpts.device
     pa = api._to_cuda(pair_a, torch.int32, dev)
     pb = api._to_cuda(pair_b, torch.int32, dev)
-    m = _run(timer, "match", lambda: _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale))
+    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer)
     g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
     # per-correspondence disparity of the previous-left keypoint (the reference looks it up in the SGBM map)
     P, n_max = g["src_idx"].shape
@@ -197,9 +204,12 @@ class CapturedPipeline:
         fn = mono_pairs if kind == "mono" else stereo_pairs
         n_total = int(n_pairs_total if n_pairs_total is not None else self.pa.numel())
 
+        scope = api.workspace_scope(f"pipeline-{id(self)}")  # private workspaces: pipelines may replay concurrently
+
         def body():
-            res = fn(self.bank, self.pa, self.pb, **kw)
-            return res, gather_records(pack_records(res), n_total)
+            with scope:
+                res = fn(self.bank, self.pa, self.pb, **kw)
+                return res, gather_records(pack_records(res), n_total)
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
