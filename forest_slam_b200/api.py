@@ -169,7 +169,8 @@ def hamming_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b
 
 # ------------------------------------------------------------------------------------------- A1
 def float_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
-    """[F, 256, n_max] fp32 channel-major (SuperPoint layout) → [F, n_max, 512] split-fp16 (hi | lo) operand bank."""
+    """[F, 256, n_max] fp32 channel-major (SuperPoint layout) → [F, n_max + 1, 512] fp16 operand bank: rows < n_max
+    are the (hi | lo) split of the descriptors, row n_max holds the frame's norm statistics (float_ops.cuh)."""
     lib = _lib.load()
     desc = _chk(desc, torch.float32, "desc")
     if desc.dim() != 3 or desc.shape[1] != 256:
@@ -177,18 +178,24 @@ def float_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
     dev = desc.device
     F, n_max = int(desc.shape[0]), int(desc.shape[2])
     counts = _chk(counts.to(dev), torch.int32, "counts")
-    ops = torch.empty((F, n_max, 512), dtype=torch.float16, device=dev)
+    ops = torch.empty((F, n_max + 1, 512), dtype=torch.float16, device=dev)
+    assert ops.numel() * 2 == lib.fs_float_operand_bytes(F, n_max) or F == 0 or n_max == 0
     _lib.check(lib.fs_float_prepare(_p(desc), F, n_max, _p(counts), _p(ops), _stream()), "fs_float_prepare")
     return ops
 
 
+FLOAT_TOP3_MAX_COLS = 4096  # fs_float_match packs the column index into 12 key bits
+
+
 def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, *, scale: float = 1.0,
                       threshold: Optional[float] = None, ratio: Optional[float] = None,
-                      operands: Optional[torch.Tensor] = None, exact_fp32: bool = False):
+                      operands: Optional[torch.Tensor] = None, exact_fp32: bool = False, split3: bool = False,
+                      want_diag: bool = False):
     """Batched float-descriptor mutual-NN (+threshold, +ratio): superglue.py:259-260, :268-278.
 
-    desc [F, 256, n_max] fp32.  The tensor-core path (default when n_max % 128 == 0) reads the split-fp16
-    operand bank (``operands`` or prepared on the fly); ``exact_fp32`` selects the CUDA-core fp32 kernel."""
+    desc [F, 256, n_max] fp32.  Default: the certified single-pass tcgen05 kernel on the fp16 operand bank
+    (``operands`` from float_prepare, or prepared on the fly); ``split3`` selects the three-MMA split-fp16 tensor-core
+    kernel, ``exact_fp32`` the CUDA-core fp32 kernel on ``desc``.  All three give the index sets of the exact score."""
     lib = _lib.load()
     if desc is not None:
         desc = _chk(desc, torch.float32, "desc")
@@ -198,7 +205,7 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
         if operands is None:
             raise ValueError("either desc or operands is required")
         dev = operands.device
-        F, n_max = int(operands.shape[0]), int(operands.shape[1])
+        F, n_max = int(operands.shape[0]), int(operands.shape[1]) - 1
     counts = _chk(counts.to(dev), torch.int32, "counts")
     a, b = _pairs(pair_a, pair_b, dev)
     P = int(a.numel())
@@ -210,21 +217,36 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
     thr = -math.inf if threshold is None else float(threshold)
     rat = float(ratio) if ratio else 0.0
     use_tc = TENSOR_CORE_MATCHER and (not exact_fp32) and n_max % 128 == 0
-    nbytes = lib.fs_float_match_tc_workspace_bytes(P, n_max) if use_tc else lib.fs_float_match_workspace_bytes(P, n_max)
-    ws = _workspace(nbytes, dev)
+    if use_tc and n_max > FLOAT_TOP3_MAX_COLS:
+        split3 = True
+    out = {"matches0": m0, "matches1": m1, "score0": sc, "second0": se, "n_matches": nm}
     if use_tc:
         if operands is None:
             operands = float_prepare(desc, counts)
-        _lib.check(lib.fs_float_match(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
-                                      rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(ws), ws.numel(),
-                                      _stream()), "fs_float_match")
+        operands = _chk(operands, torch.float16, "operands")
+        if tuple(operands.shape) != (F, n_max + 1, 512):
+            raise ValueError("operands must be the [n_frames, n_max + 1, 512] fp16 bank float_prepare returns")
+        if split3:
+            ws = _workspace(lib.fs_float_match_split3_workspace_bytes(P, n_max), dev)
+            _lib.check(lib.fs_float_match_split3(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
+                                                 rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(ws), ws.numel(),
+                                                 _stream()), "fs_float_match_split3")
+        else:
+            ws = _workspace(lib.fs_float_match_tc_workspace_bytes(P, n_max), dev)
+            diag = torch.zeros((4,), dtype=torch.int32, device=dev) if want_diag else None
+            _lib.check(lib.fs_float_match(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
+                                          rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(diag), _p(ws), ws.numel(),
+                                          _stream()), "fs_float_match")
+            if want_diag:
+                out["diag"] = diag
     else:
         if desc is None:
             raise ValueError("the fp32 kernel needs desc")
+        ws = _workspace(lib.fs_float_match_workspace_bytes(P, n_max), dev)
         _lib.check(lib.fs_float_match_fp32(_p(desc), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
                                            rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(ws), ws.numel(),
                                            _stream()), "fs_float_match_fp32")
-    return {"matches0": m0, "matches1": m1, "score0": sc, "second0": se, "n_matches": nm}
+    return out
 
 
 # ------------------------------------------------------------------------------------------- A3
@@ -517,7 +539,8 @@ class BFMatcher:
 
 
 def match_mutual_nn(descriptors0, descriptors1, *, scale: float = 1.0, threshold: Optional[float] = None,
-                    ratio: Optional[float] = None, exact_fp32: bool = False):
+                    ratio: Optional[float] = None, exact_fp32: bool = False, split3: bool = False,
+                    want_diag: bool = False):
     """Tail of SuperGlue.forward on the raw contraction (superglue.py:259-260, :268-278).
 
     descriptors0 [256, N0], descriptors1 [256, N1] float32 (SuperPoint layout) →
@@ -535,14 +558,17 @@ def match_mutual_nn(descriptors0, descriptors1, *, scale: float = 1.0, threshold
     bank[1, :, :n1] = _to_cuda(d1, torch.float32, dev)
     counts = torch.tensor([n0, n1], dtype=torch.int32, device=dev)
     r = float_match_batch(bank, counts, [0], [1], scale=scale, threshold=threshold, ratio=ratio,
-                          exact_fp32=exact_fp32)
+                          exact_fp32=exact_fp32, split3=split3, want_diag=want_diag)
     m0 = r["matches0"][0, :n0].cpu().numpy().astype(np.int64)
     m1 = r["matches1"][0, :n1].cpu().numpy().astype(np.int64)
     s0 = r["score0"][0, :n0].cpu().numpy()
     ms0 = np.where(m0 >= 0, s0, 0.0).astype(np.float32)
     ms1 = np.zeros((n1,), np.float32)
     ms1[m0[m0 >= 0]] = ms0[m0 >= 0]
-    return {"matches0": m0, "matches1": m1, "matching_scores0": ms0, "matching_scores1": ms1}
+    out = {"matches0": m0, "matches1": m1, "matching_scores0": ms0, "matching_scores1": ms1}
+    if want_diag and "diag" in r:
+        out["diag"] = r["diag"].cpu().numpy()
+    return out
 
 
 def _corr_batch(p0, p1, dev):

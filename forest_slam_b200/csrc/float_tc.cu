@@ -20,39 +20,83 @@
 //            (order independent => deterministic; lowest index wins ties).
 #include <cuda.h>
 #include <cuda_fp16.h>
-#include "float_common.cuh"
+#include "float_ops.cuh"
 #include "sm100_ptx.cuh"
 
 namespace {
 
 using namespace sm100;
 
-// [F, 256, n_max] fp32 channel-major  ->  [F, n_max, 512] fp16, row = [hi(256) | lo(256)].
-// Transposes through shared memory so that both the read (along n) and the write (along k) are coalesced.
+// [F, 256, n_max] fp32 channel-major  ->  [F, n_max + 1, 512] fp16, row = [hi(256) | lo(256)], last row = statistics.
+// One block = 32 keypoints x all 256 channels, in four passes of 64 channels through shared memory so that the read
+// (along n) and the write (along k, half2 per lane = 128 B per warp) are both coalesced.  The per-row sums of hi^2
+// and lo^2 are accumulated in a fixed order; their frame maxima go to the statistics row (float_ops.cuh).
 __global__ void __launch_bounds__(256)
 k_float_prepare(const float* __restrict__ desc, int n_max, const int32_t* __restrict__ counts,
                 __half* __restrict__ ops) {
-    __shared__ float tile[32][33];
-    const int f = blockIdx.z;
-    const int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+    __shared__ float tile[64][33];
+    __shared__ float red[2][8];
+    const int f = blockIdx.y;
+    const int n0 = blockIdx.x * 32;
     const int cnt = min(counts[f], n_max);
     const float* src = desc + (size_t)f * FS_FLOAT_DIM * n_max;
-    __half* dst = ops + (size_t)f * n_max * 512;
-    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
-    for (int r = ty; r < 32; r += 8) {
-        const int n = n0 + tx;
-        tile[r][tx] = (n < cnt) ? src[(size_t)(k0 + r) * n_max + n] : 0.f;
+    __half* dst = ops + (size_t)f * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    float h2[4] = {0.f, 0.f, 0.f, 0.f}, l2[4] = {0.f, 0.f, 0.f, 0.f};  // rows warp*4 + i, this lane's channels
+    for (int kt = 0; kt < FS_FLOAT_DIM / 64; kt++) {
+        __syncthreads();
+        for (int r = warp; r < 64; r += 8) {
+            const int n = n0 + lane;
+            tile[r][lane] = (n < cnt) ? src[(size_t)(kt * 64 + r) * n_max + n] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int rl = warp * 4 + i, n = n0 + rl;
+            if (n >= n_max) continue;
+            const float x0 = tile[2 * lane][rl], x1 = tile[2 * lane + 1][rl];
+            const __half hi0 = __float2half_rn(x0), hi1 = __float2half_rn(x1);
+            const __half lo0 = __float2half_rn(x0 - __half2float(hi0)), lo1 = __float2half_rn(x1 - __half2float(hi1));
+            __half2* out = reinterpret_cast<__half2*>(dst + (size_t)n * fs::OP_ROW_HALFS + kt * 64) + lane;
+            out[0] = __halves2half2(hi0, hi1);
+            out[128] = __halves2half2(lo0, lo1);  // + 256 halfs
+            const float a0 = __half2float(hi0), a1 = __half2float(hi1), b0 = __half2float(lo0), b1 = __half2float(lo1);
+            h2[i] = fmaf(a1, a1, fmaf(a0, a0, h2[i]));
+            l2[i] = fmaf(b1, b1, fmaf(b0, b0, l2[i]));
+        }
+    }
+    float mh = 0.f, ml = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        float a = h2[i], b = l2[i];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o);
+            b += __shfl_xor_sync(0xffffffffu, b, o);
+        }
+        mh = fmaxf(mh, a);
+        ml = fmaxf(ml, b);
+    }
+    if (lane == 0) {
+        red[0][warp] = mh;
+        red[1][warp] = ml;
     }
     __syncthreads();
-    for (int r = ty; r < 32; r += 8) {
-        const int n = n0 + r;
-        if (n >= n_max) continue;
-        const float x = tile[tx][r];
-        const __half hi = __float2half_rn(x);
-        const __half lo = __float2half_rn(x - __half2float(hi));
-        dst[(size_t)n * 512 + k0 + tx] = hi;
-        dst[(size_t)n * 512 + 256 + k0 + tx] = lo;
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) {
+            mh = fmaxf(mh, red[0][w]);
+            ml = fmaxf(ml, red[1][w]);
+        }
+        unsigned int* st = reinterpret_cast<unsigned int*>(dst + (size_t)n_max * fs::OP_ROW_HALFS);
+        atomicMax(st, __float_as_uint(mh));
+        atomicMax(st + 1, __float_as_uint(ml));
     }
+}
+
+// zero the statistics rows before k_float_prepare accumulates its maxima
+__global__ void k_float_prepare_clear(int n_max, __half* __restrict__ ops) {
+    uint4* row = reinterpret_cast<uint4*>(ops + ((size_t)blockIdx.x * fs::op_rows(n_max) + n_max) * fs::OP_ROW_HALFS);
+    if (threadIdx.x < fs::OP_ROW_BYTES / 16) row[threadIdx.x] = make_uint4(0, 0, 0, 0);
 }
 
 // ------------------------------------------------------------------------------------------------ main kernel
@@ -260,6 +304,9 @@ k_unpack_cols(const unsigned long long* __restrict__ col_best, size_t n, int32_t
     idx1[i] = k ? (int32_t)(0xFFFFFFFFu - (uint32_t)(k & 0xFFFFFFFFull)) : -1;
 }
 
+}  // namespace
+
+namespace fs {
 typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                         CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -276,9 +323,9 @@ int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMa
         }
         fn = (PFN_tmapEncodeTiled)sym;
     }
-    const cuuint64_t gdim[3] = {512, (cuuint64_t)n_max, (cuuint64_t)n_frames};
-    const cuuint64_t gstride[2] = {512 * 2, (cuuint64_t)n_max * 512 * 2};
-    const cuuint32_t box[3] = {TC_BK, TC_BM, 1};
+    const cuuint64_t gdim[3] = {512, (cuuint64_t)fs::op_rows(n_max), (cuuint64_t)n_frames};
+    const cuuint64_t gstride[2] = {512 * 2, (cuuint64_t)fs::op_rows(n_max) * 512 * 2};
+    const cuuint32_t box[3] = {64, 128, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(operands), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -290,7 +337,7 @@ int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMa
     return FS_OK;
 }
 
-}  // namespace
+}  // namespace fs
 
 extern "C" int fs_float_prepare(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
                                 void* operands, fs_stream_t stream) {
@@ -298,20 +345,22 @@ extern "C" int fs_float_prepare(const float* desc_f32, int n_frames, int n_max, 
     if (n_frames == 0 || n_max == 0) return FS_OK;
     FS_REQUIRE(desc_f32 && counts && operands, "null pointer");
     FS_REQUIRE(n_frames <= 65535, "n_frames too large for one launch");
-    dim3 grid((n_max + 31) / 32, FS_FLOAT_DIM / 32, n_frames);
+    k_float_prepare_clear<<<n_frames, 64, 0, (cudaStream_t)stream>>>(n_max, (__half*)operands);
+    FS_LAUNCH_CHECK("k_float_prepare_clear");
+    dim3 grid((n_max + 31) / 32, n_frames);
     k_float_prepare<<<grid, 256, 0, (cudaStream_t)stream>>>(desc_f32, n_max, counts, (__half*)operands);
     FS_LAUNCH_CHECK("k_float_prepare");
     return FS_OK;
 }
 
-extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
+extern "C" size_t fs_float_match_split3_workspace_bytes(int n_pairs, int n_max) {
     if (n_pairs <= 0 || n_max <= 0) return 256;
     const size_t n = (size_t)n_pairs * n_max;
     // best, second, idx0, idx1 (4 B each) + packed column keys (8 B)
     return 4 * fs::align_up(n * 4, 256) + fs::align_up(n * 8, 256) + 256;
 }
 
-extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, const int32_t* counts,
+extern "C" int fs_float_match_split3(const void* operands, int n_frames, int n_max, const int32_t* counts,
                               const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float threshold,
                               float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
                               int32_t* n_matches, void* workspace, size_t workspace_bytes, fs_stream_t stream_) {
@@ -320,13 +369,13 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
     if (n_pairs == 0 || n_max == 0) return FS_OK;
     FS_REQUIRE(operands && counts && pair_a && pair_b && matches0, "null pointer");
     FS_REQUIRE(((uintptr_t)operands & 15) == 0, "operands must be 16-byte aligned");
-    const size_t need = fs_float_match_tc_workspace_bytes(n_pairs, n_max);
+    const size_t need = fs_float_match_split3_workspace_bytes(n_pairs, n_max);
     if (!workspace || workspace_bytes < need) {
-        fs::set_error("fs_float_match: workspace %zu < %zu", workspace_bytes, need);
+        fs::set_error("fs_float_match_split3: workspace %zu < %zu", workspace_bytes, need);
         return FS_ERR_WORKSPACE;
     }
     CUtensorMap tmap;
-    int st = encode_operand_map(operands, n_frames, n_max, &tmap);
+    int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
     if (st != FS_OK) return st;
     fs::Carver ws(workspace);
     const size_t n = (size_t)n_pairs * n_max;

@@ -1,0 +1,478 @@
+// float_top3.cu — A1 (float descriptor mutual-NN, superglue.py:259-260, :268-278) as ONE fp16 tensor-core pass per
+// direction with certified results.
+//
+// Why: the split-fp16 kernel (float_tc.cu) needs three MMAs per k-step to be fp32-grade and a cross-lane column
+// reduction in its epilogue; both cap it at ~20 % of the algorithmic tensor roofline.  Here the contraction runs ONCE
+// on the hi halves (fp16 x fp16 -> fp32 in TMEM), once per direction (rows of a against b, rows of b against a: the
+// column side of superglue.py:268 becomes a row problem, so the epilogue never leaves the thread), and the epilogue
+// keeps each row's TOP-3 packed keys.  A rigorous bound delta on |exact - tensor-core score| (float_ops.cuh) then
+// decides, row by row, what the approximate keys already prove:
+//   best - second  > 2 delta : the arg-max is certain;
+//   best - third   > 2 delta : the arg-max is one of two columns -> both are rescored exactly (fp32, hi + lo);
+//   otherwise                : the row is rescanned exactly over all columns (rare: k_float_fullscan).
+// The same interval test guards the threshold and the ratio decisions.  Index sets are therefore those of the exact
+// score, never of the fp16 one; score values are exact where a decision depended on them and within delta elsewhere.
+//
+// k_float_top3_tc — one CTA = (direction, frame pair, 256-row block of the "row" frame), 320 threads:
+//   warp 8    : TMA producer.  The row block (2 x 128 rows x 256 fp16 = 128 KB) is loaded once and stays resident;
+//               the other frame streams through a 4-stage ring of [128 x 64] boxes (16 KB, 128-byte swizzle);
+//   warp 9    : MMA issuer: per 128-column tile 2 x 16 tcgen05.mma (128x128x16, kind::f16) into two of four TMEM
+//               accumulators (2 row halves x double buffer = 512 columns); tcgen05.commit frees ring stages / publishes;
+//   warps 0-7 : epilogue, thread = row: tcgen05.ld 32x32b, key = bits(fma(v, sc, bias)) * 4096 + (4095 - col)  (FMA
+//               pipe), top-3 by a min/max merge network on the keys (ALU pipe, 4 ops per element).
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include "float_ops.cuh"
+#include "sm100_ptx.cuh"
+
+namespace {
+
+using namespace sm100;
+
+constexpr int T3_BN = 128, T3_BK = 64, T3_KCH = FS_FLOAT_DIM / T3_BK;  // 4 k-chunks of 64
+constexpr int T3_ROWS = 256;                                          // rows per CTA (two MMA halves of 128)
+constexpr int T3_STAGES = 4;
+constexpr int T3_THREADS = 320;
+constexpr int T3_TMA_WARP = 8, T3_MMA_WARP = 9;  // warps 0..7 are the epilogue
+static_assert(T3_STAGES == T3_KCH, "the ring is indexed by k-chunk");
+constexpr int T3_BOX_BYTES = 128 * T3_BK * 2;               // 16 KB: one [128 x 64] fp16 box
+constexpr int T3_A_BYTES = 2 * T3_KCH * T3_BOX_BYTES;       // 128 KB
+constexpr int T3_TMEM_COLS = 512;
+constexpr uint32_t T3_IDESC = make_idesc_f16(128, T3_BN, /*F16*/ 0);
+
+struct T3Barriers {
+    uint64_t a_full;
+    uint64_t full[T3_STAGES], empty[T3_STAGES];
+    uint64_t tmem_full[2], tmem_empty[2];
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_BOX_BYTES + 256 /*barriers*/;
+
+// merge the sorted pair (hi >= lo) of two new keys into the running sorted triple (k1 >= k2 >= k3)
+__device__ __forceinline__ void top3_push2(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t e0, uint32_t e1) {
+    const uint32_t hi = max(e0, e1), lo = min(e0, e1);
+    const uint32_t m1 = min(k1, hi);
+    const uint32_t n3 = __vimax3_u32(k3, min(k2, hi), min(k1, lo));
+    const uint32_t n2 = __vimax3_u32(m1, k2, lo);
+    k1 = max(k1, hi);
+    k2 = n2;
+    k3 = n3;
+}
+
+// merge the sorted triple (t1 >= t2 >= t3) into the running sorted triple
+__device__ __forceinline__ void top3_merge3(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t t1, uint32_t t2,
+                                            uint32_t t3) {
+    const uint32_t n3 = max(__vimax3_u32(k3, t3, min(k2, t1)), min(k1, t2));
+    const uint32_t n2 = __vimax3_u32(k2, t2, min(k1, t1));
+    k1 = max(k1, t1);
+    k2 = n2;
+    k3 = n3;
+}
+
+__global__ void __launch_bounds__(T3_THREADS, 1)
+k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const void* __restrict__ operands, int n_max,
+                const int32_t* __restrict__ counts, const int32_t* __restrict__ pair_a,
+                const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0, uint32_t key_mul, uint4* __restrict__ keys) {
+    // key_mul = 4096 comes in as an argument so that bits * key_mul + idx stays an IMAD (FMA pipe) instead of being
+    // strength-reduced to a shift-add on the ALU pipe, which the top-3 network already saturates
+    const int p = pair0 + blockIdx.y, dir = blockIdx.z;
+    const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
+    const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
+    const int m0 = blockIdx.x * T3_ROWS;
+    if (m0 >= n0) return;
+    const int ntiles = (n1 + T3_BN - 1) / T3_BN;
+    const int nhalf = (m0 + 128 < n0) ? 2 : 1;  // the second 128-row half may be empty
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;                 // [half][kc] boxes of 16 KB
+    uint8_t* sB = smem + T3_A_BYTES;    // [stage] boxes of 16 KB
+    T3Barriers& bar = *reinterpret_cast<T3Barriers*>(sB + T3_STAGES * T3_BOX_BYTES);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        prefetch_tensormap(&tmap);
+        mbar_init(&bar.a_full, 1);
+        for (int s = 0; s < T3_STAGES; s++) {
+            mbar_init(&bar.full[s], 1);
+            mbar_init(&bar.empty[s], 1);
+        }
+        for (int b = 0; b < 2; b++) {
+            mbar_init(&bar.tmem_full[b], 1);
+            mbar_init(&bar.tmem_empty[b], 4 * nhalf);
+        }
+        fence_barrier_init();
+    }
+    if (warp == T3_MMA_WARP) {
+        tmem_alloc(&bar.tmem_base, T3_TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = bar.tmem_base;
+
+    if (warp == T3_TMA_WARP) {
+        // ===================================================== TMA producer (one thread)
+        if (lane == 0 && ntiles > 0) {
+            mbar_arrive_expect_tx(&bar.a_full, nhalf * T3_KCH * T3_BOX_BYTES);
+            for (int h = 0; h < nhalf; h++)
+                for (int kc = 0; kc < T3_KCH; kc++)
+                    tma_load_3d(sA + (h * T3_KCH + kc) * T3_BOX_BYTES, &tmap, &bar.a_full, kc * T3_BK, m0 + h * 128, fa);
+            // ring stage == k-chunk (T3_STAGES == T3_KCH): stage kc is refilled once per tile, phase = tile parity
+            for (int t = 0; t < ntiles; t++) {
+#pragma unroll
+                for (int kc = 0; kc < T3_KCH; kc++) {
+                    mbar_wait(&bar.empty[kc], (t & 1) ^ 1);
+                    mbar_arrive_expect_tx(&bar.full[kc], T3_BOX_BYTES);
+                    tma_load_3d(sB + kc * T3_BOX_BYTES, &tmap, &bar.full[kc], kc * T3_BK, t * T3_BN, fb);
+                }
+            }
+        }
+    } else if (warp == T3_MMA_WARP) {
+        // ===================================================== MMA issuer (one thread).  This warp has the highest warp id
+        // of the CTA: the sub-partition's arbiter prefers it over the two epilogue warps it shares issue slots with, so
+        // the tensor pipe is never starved by the ALU-bound epilogue (measured: with the issuer as warp 1 the MMAs and
+        // the epilogue of consecutive tiles ran back to back instead of overlapped).
+        if (lane == 0 && ntiles > 0) {
+            mbar_wait(&bar.a_full, 0);
+            tc_fence_after();
+            const uint64_t a_desc0 = make_desc_k_sw128(smem_u32(sA)), b_desc0 = make_desc_k_sw128(smem_u32(sB));
+            for (int t = 0; t < ntiles; t++) {
+                const int buf = t & 1;
+                mbar_wait(&bar.tmem_empty[buf], ((t >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d0 = tmem_base + (buf * 2) * T3_BN;
+#pragma unroll
+                for (int kc = 0; kc < T3_KCH; kc++) {
+                    mbar_wait(&bar.full[kc], t & 1);
+                    tc_fence_after();
+#pragma unroll
+                    for (int ks = 0; ks < T3_BK / 16; ks++) {
+                        // descriptor start-address field is in 16-byte units: +2 per K = 16 step inside the swizzle row
+                        const uint64_t bd = b_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                        const uint64_t ad = a_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                        umma_f16(d0, ad, bd, T3_IDESC, (kc | ks) != 0);
+                        if (nhalf == 2)
+                            umma_f16(d0 + T3_BN, ad + (uint64_t)((T3_KCH * T3_BOX_BYTES) >> 4), bd, T3_IDESC, (kc | ks) != 0);
+                    }
+                    umma_commit(&bar.empty[kc]);  // ring stage free once these MMAs have read it
+                }
+                umma_commit(&bar.tmem_full[buf]);  // both accumulators of this tile complete
+            }
+        }
+    } else {
+        // ===================================================== epilogue: warps 0..7, thread = row
+        const int half = warp >> 2;
+        const int quarter = warp & 3;  // the TMEM lane quarter this warp may read
+        if (half < nhalf) {
+            const int row = m0 + half * 128 + quarter * 32 + lane;
+            const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
+            const float sc = ps.sc;
+            uint32_t k1 = 0, k2 = 0, k3 = 0;
+            for (int t = 0; t < ntiles; t++) {
+                const int buf = t & 1;
+                mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
+                tc_fence_after();
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN;
+                // two register sets: the TMEM load of chunk c + 1 is in flight while chunk c goes through the network
+                uint32_t ra[32], rb[32];
+                tmem_ld_32x32b_x32(taddr, ra);
+#pragma unroll
+                for (int c = 0; c < T3_BN / 32; c++) {
+                    uint32_t* r = (c & 1) ? rb : ra;
+                    tmem_ld_wait();
+                    if (c + 1 < T3_BN / 32) {
+                        tmem_ld_32x32b_x32(taddr + (c + 1) * 32, (c & 1) ? ra : rb);
+                    } else {  // accumulator fully read: hand it back to the MMA warp
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                    }
+                    // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's own top-3 is
+                    // shifted to the global column afterwards and merged into the running triple (3 + 7 ops per 32 columns)
+                    const int col0 = t * T3_BN + c * 32;
+                    const int nvalid = n1 - col0;
+                    uint32_t l1 = 0, l2 = 0, l3 = 0;
+                    if (nvalid >= 32) {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            const uint32_t e0 = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul +
+                                                (uint32_t)(4095 - j);
+                            const uint32_t e1 = __float_as_uint(fmaf(__uint_as_float(r[j + 1]), sc, fs::KEY_BIAS)) * key_mul +
+                                                (uint32_t)(4094 - j);
+                            top3_push2(l1, l2, l3, e0, e1);
+                        }
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 32; j += 2) {
+                            uint32_t e0 = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul +
+                                          (uint32_t)(4095 - j);
+                            uint32_t e1 = __float_as_uint(fmaf(__uint_as_float(r[j + 1]), sc, fs::KEY_BIAS)) * key_mul +
+                                          (uint32_t)(4094 - j);
+                            e0 = (j < nvalid) ? e0 : 0u;
+                            e1 = (j + 1 < nvalid) ? e1 : 0u;
+                            top3_push2(l1, l2, l3, e0, e1);
+                        }
+                    }
+                    // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; empty slots stay 0
+                    l1 -= l1 ? (uint32_t)col0 : 0u;
+                    l2 -= l2 ? (uint32_t)col0 : 0u;
+                    l3 -= l3 ? (uint32_t)col0 : 0u;
+                    top3_merge3(k1, k2, k3, l1, l2, l3);
+                }
+            }
+            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(k1, k2, k3, 0u);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == T3_MMA_WARP) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, T3_TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------ resolve
+// Lowe ratio decision exactly as k_float_finalize evaluates it (float_fp32.cu): monotone in both arguments
+__device__ __forceinline__ bool ratio_pass(float b, float s, float ratio) {
+    const float db = __fsqrt_rn(fmaxf(0.f, __fsub_rn(2.f, __fmul_rn(2.f, b))));
+    const float ds = __fsqrt_rn(fmaxf(0.f, __fsub_rn(2.f, __fmul_rn(2.f, s))));
+    return db < __fmul_rn(ratio, ds);
+}
+
+struct T3Out {
+    float* best;     // [2][P][n_max]  direction 0 = rows of a, direction 1 = rows of b
+    float* second;
+    int32_t* idx;
+    uint32_t* list;  // rows that need the exact full scan: (dir << 31) | (p * n_max + row)
+    int32_t* counters;  // [0] full scans, [1] rows with rescored candidates
+};
+
+// thread = (direction, pair, row): decode the top-3 keys, decide what they prove, rescore what they do not
+__global__ void __launch_bounds__(256)
+k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
+                const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
+                const uint4* __restrict__ keys, float scale, float threshold, float ratio, T3Out out) {
+    const int p = pair0 + blockIdx.y, dir = blockIdx.z;
+    const int row = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
+    const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
+    const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
+    if ((row & ~31) >= n0 || n1 <= 0) return;  // (warp-uniform)
+    const bool active = row < n0;
+    const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
+    const size_t o = ((size_t)dir * n_pairs_total + p) * n_max + row;
+    float v1 = -INFINITY, v2 = -INFINITY, v3 = -INFINITY;
+    int i1 = 0, i2 = 0;
+    bool amb_idx = false, want1 = false, want2 = false, full = false;
+    if (active) {
+        const uint4 k = keys[o];
+        v1 = fs::key_score(k.x, ps);
+        v2 = fs::key_score(k.y, ps);
+        v3 = fs::key_score(k.z, ps);
+        i1 = fs::key_col(k.x);
+        i2 = fs::key_col(k.y);
+        const float d2 = 2.f * ps.delta;
+        amb_idx = !(v1 - v2 > d2);
+        const bool second_sure = (v2 - v3 > d2);  // the runner-up is certainly column i2
+        if (amb_idx) {
+            if (v1 - v3 > d2) want1 = want2 = true;  // the arg-max is i1 or i2
+            else full = true;
+        }
+        if (dir == 0) {
+            if (isfinite(threshold) && fabsf(v1 * scale - threshold) <= ps.delta * fabsf(scale) * 1.001f + 1e-12f)
+                want1 = true;
+            if (ratio > 0.f && k.y != 0u) {
+                const bool undecided = amb_idx || (ratio_pass(v1 + ps.delta, v2 - ps.delta, ratio) !=
+                                                   ratio_pass(v1 - ps.delta, v2 + ps.delta, ratio));
+                if (undecided) {
+                    if (second_sure) want1 = want2 = true;
+                    else full = true;
+                }
+            }
+        }
+    }
+    // warp-cooperative exact rescoring of the flagged rows' candidates (float_ops.cuh: warp_dot)
+    const __half* bank_a = static_cast<const __half*>(operands) + (size_t)fa * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+    const __half* bank_b = static_cast<const __half*>(operands) + (size_t)fb * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+    float ex1 = 0.f, ex2 = 0.f;
+    unsigned jobs = __ballot_sync(0xffffffffu, active && !full && (want1 || want2));
+    if (jobs && lane == 0) atomicAdd(out.counters + 1, __popc(jobs));
+    while (jobs) {
+        const int l = __ffs(jobs) - 1;
+        jobs &= jobs - 1;
+        const int r_ = __shfl_sync(0xffffffffu, row, l);
+        const int c1 = __shfl_sync(0xffffffffu, i1, l), c2 = __shfl_sync(0xffffffffu, i2, l);
+        const bool w2 = __shfl_sync(0xffffffffu, (int)want2, l) != 0;
+        const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)r_ * fs::OP_ROW_HALFS, lane);
+        const float e1 = fs::warp_dot(a, fs::load_op_row(bank_b + (size_t)c1 * fs::OP_ROW_HALFS, lane));
+        float e2 = 0.f;
+        if (w2) e2 = fs::warp_dot(a, fs::load_op_row(bank_b + (size_t)c2 * fs::OP_ROW_HALFS, lane));
+        if (lane == l) {
+            ex1 = e1;
+            ex2 = e2;
+        }
+    }
+    if (!active) return;
+    float b = v1, s = v2;
+    int ib = i1;
+    if (!full) {
+        if (want1) b = ex1;
+        if (want2) {
+            s = ex2;
+            if (amb_idx && fs::better(ex2, i2, ex1, i1)) {
+                b = ex2;
+                ib = i2;
+                s = ex1;
+            }
+        }
+    } else {
+        const int pos = atomicAdd(out.counters, 1);
+        out.list[pos] = ((uint32_t)dir << 31) | (uint32_t)((size_t)p * n_max + row);
+    }
+    out.best[o] = b;
+    out.second[o] = s;
+    out.idx[o] = ib;
+}
+
+// exact top-2 over ALL columns for the rows the keys could not decide; one CTA per listed row
+__global__ void __launch_bounds__(256)
+k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
+                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, T3Out out) {
+    __shared__ float s_best[8], s_second[8];
+    __shared__ int s_idx[8];
+    const int count = out.counters[0];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int e = blockIdx.x; e < count; e += gridDim.x) {
+        const uint32_t ent = out.list[e];
+        const int dir = ent >> 31;
+        const uint32_t lin = ent & 0x7FFFFFFFu;
+        const int p = lin / n_max, row = lin % n_max;
+        const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
+        const int n1 = min(counts[fb], n_max);
+        const __half* bank_a = static_cast<const __half*>(operands) + (size_t)fa * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+        const __half* bank_b = static_cast<const __half*>(operands) + (size_t)fb * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+        const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)row * fs::OP_ROW_HALFS, lane);
+        fs::Top2 t;
+        t.init();
+        for (int c = warp; c < n1; c += 8)
+            t.push(fs::warp_dot(a, fs::load_op_row(bank_b + (size_t)c * fs::OP_ROW_HALFS, lane)), c);
+        __syncthreads();  // the previous entry's merge is done with the staging arrays
+        if (lane == 0) {
+            s_best[warp] = t.best;
+            s_second[warp] = t.second;
+            s_idx[warp] = t.idx;
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            fs::Top2 m;
+            m.init();
+            for (int w = 0; w < 8; w++) m.merge(s_best[w], s_second[w], s_idx[w]);
+            const size_t o = ((size_t)dir * n_pairs_total + p) * n_max + row;
+            out.best[o] = m.best;
+            out.second[o] = m.second;
+            out.idx[o] = m.idx;
+        }
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------ C ABI
+extern "C" size_t fs_float_operand_bytes(int n_frames, int n_max) {
+    if (n_frames <= 0 || n_max <= 0) return 0;
+    return (size_t)n_frames * fs::op_rows(n_max) * fs::OP_ROW_BYTES;
+}
+
+extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
+    if (n_pairs <= 0 || n_max <= 0) return 256;
+    const size_t n2 = 2 * (size_t)n_pairs * n_max;
+    // keys (16 B) + best, second, idx, list (4 B each) for both directions + counters
+    return fs::align_up(n2 * 16, 256) + 4 * fs::align_up(n2 * 4, 256) + 256 + 256;
+}
+
+// the tensor-core pass alone: top-3 keys of every row of both directions
+static int launch_top3(const CUtensorMap& tmap, const void* operands, int n_max, const int32_t* counts,
+                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream) {
+    static int granted[64];
+    const int st_ = fs::ensure_dyn_smem(k_float_top3_tc, granted, (size_t)(T3_SMEM_BYTES));
+    if (st_ != FS_OK) return st_;
+    for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
+        const int np = min(32768, n_pairs - p0);
+        dim3 grid((n_max + T3_ROWS - 1) / T3_ROWS, np, 2);
+        k_float_top3_tc<<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs,
+                                                                     p0, 4096u, keys);
+        FS_LAUNCH_CHECK("k_float_top3_tc");
+    }
+    return FS_OK;
+}
+
+// Measurement hook (bench.py roofline): ONLY the tensor-core kernel of fs_float_match, same grid, keys into `workspace`
+extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                                  const int32_t* pair_a, const int32_t* pair_b, int n_pairs, void* workspace,
+                                  size_t workspace_bytes, fs_stream_t stream_) {
+    FS_REQUIRE(n_pairs > 0 && n_frames > 0 && n_max > 0 && n_max <= fs::KEY_MAX_COLS, "bad size");
+    FS_REQUIRE(operands && counts && pair_a && pair_b, "null pointer");
+    if (!workspace || workspace_bytes < fs_float_match_tc_workspace_bytes(n_pairs, n_max)) {
+        fs::set_error("fs_float_top3_keys: workspace too small");
+        return FS_ERR_WORKSPACE;
+    }
+    CUtensorMap tmap;
+    const int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    if (st != FS_OK) return st;
+    fs::Carver ws(workspace);
+    return launch_top3(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs,
+                       ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_);
+}
+
+extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                              const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float threshold,
+                              float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
+                              int32_t* n_matches, int32_t* diag, void* workspace, size_t workspace_bytes,
+                              fs_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    FS_REQUIRE(n_pairs >= 0 && n_frames >= 0 && n_max >= 0, "negative size");
+    if (n_pairs == 0 || n_max == 0) return FS_OK;
+    FS_REQUIRE(operands && counts && pair_a && pair_b && matches0, "null pointer");
+    FS_REQUIRE(((uintptr_t)operands & 15) == 0, "operands must be 16-byte aligned");
+    FS_REQUIRE(scale > 0.f, "scale must be positive");
+    if (n_max > fs::KEY_MAX_COLS) {
+        fs::set_error("fs_float_match: n_max %d > %d (use fs_float_match_split3)", n_max, fs::KEY_MAX_COLS);
+        return FS_ERR_UNSUPPORTED;
+    }
+    FS_REQUIRE((size_t)n_pairs * n_max < (1ull << 31), "n_pairs * n_max too large for one call");
+    const size_t need = fs_float_match_tc_workspace_bytes(n_pairs, n_max);
+    if (!workspace || workspace_bytes < need) {
+        fs::set_error("fs_float_match: workspace %zu < %zu", workspace_bytes, need);
+        return FS_ERR_WORKSPACE;
+    }
+    CUtensorMap tmap;
+    int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    if (st != FS_OK) return st;
+    fs::Carver ws(workspace);
+    const size_t n = (size_t)n_pairs * n_max, n2 = 2 * n;
+    uint4* keys = ws.take<uint4>(n2);
+    T3Out out;
+    out.best = ws.take<float>(n2);
+    out.second = ws.take<float>(n2);
+    out.idx = ws.take<int32_t>(n2);
+    out.list = ws.take<uint32_t>(n2);
+    out.counters = ws.take<int32_t>(64);
+    FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));
+    st = launch_top3(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
+    if (st != FS_OK) return st;
+    for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
+        const int np = min(32768, n_pairs - p0);
+        dim3 rgrid((n_max + 255) / 256, np, 2);
+        k_float_resolve<<<rgrid, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, p0, keys, scale,
+                                                   threshold, ratio, out);
+        FS_LAUNCH_CHECK("k_float_resolve");
+    }
+    k_float_fullscan<<<fs::sm_count() * 4, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out);
+    FS_LAUNCH_CHECK("k_float_fullscan");
+    if (diag) FS_CUDA(cudaMemcpyAsync(diag, out.counters, 4 * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
+    fs::FloatRowTop2 d0{out.best, out.second, out.idx};
+    return fs::launch_float_finalize(n_max, counts, pair_a, pair_b, n_pairs, d0, out.idx + n, scale, threshold, ratio,
+                                     matches0, score0, second0, matches1, n_matches, stream);
+}

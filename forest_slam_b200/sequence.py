@@ -26,7 +26,7 @@ class FrameBank:
     desc_f32: Optional[torch.Tensor] = None  # [F, 256, n_max] f32 (SuperPoint layout)
     desc_bin: Optional[torch.Tensor] = None  # [F, n_max, 32] u8 (ORB layout)
     disparity: Optional[torch.Tensor] = None  # [F, n_max] f32 per-keypoint disparity (uL - uR)
-    operands: Optional[torch.Tensor] = None  # [F, n_max, 512] fp16 hi|lo split operands of the tensor-core matcher
+    operands: Optional[torch.Tensor] = None  # [F, n_max + 1, 512] fp16 operand bank (api.float_prepare) of the tensor-core matcher
 
     @staticmethod
     def from_numpy(kpts, counts, desc_f32=None, desc_bin=None, disparity=None, device="cuda") -> "FrameBank":
@@ -69,18 +69,18 @@ def _run(timer, name, fn):
 
 
 def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp32: bool, scale: float = 1.0,
-           timer=None):
+           timer=None, split3: bool = False):
     if descriptor == "float":
         if bank.desc_f32 is None and bank.operands is None:
             raise ValueError("the frame bank holds no float descriptors")
         operands = bank.operands
-        n_max = int(bank.desc_f32.shape[2]) if bank.desc_f32 is not None else int(bank.operands.shape[1])
+        n_max = int(bank.desc_f32.shape[2]) if bank.desc_f32 is not None else int(bank.operands.shape[1]) - 1
         if operands is None and not exact_fp32 and api.TENSOR_CORE_MATCHER and n_max % 128 == 0:
             # fp32 channel-major descriptors -> split-fp16 operand rows, once per frame (not per pair)
             operands = _run(timer, "prepare", lambda: api.float_prepare(bank.desc_f32, bank.counts))
         r = _run(timer, "match", lambda: api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale,
                                                                threshold=threshold, ratio=ratio, operands=operands,
-                                                               exact_fp32=exact_fp32))
+                                                               exact_fp32=exact_fp32, split3=split3))
     elif descriptor == "binary":
         if bank.desc_bin is None:
             raise ValueError("the frame bank holds no binary descriptors")
@@ -93,14 +93,14 @@ def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp3
 
 def mono_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "float", camera: ForestCamera = ForestCamera(),
                threshold: Optional[float] = None, ratio: Optional[float] = None, prob: float = 0.999,
-               ransac_threshold: float = 1.0, max_iters: int = 1000, exact_fp32: bool = False, scale: float = 1.0,
+               ransac_threshold: float = 1.0, max_iters: int = 1000, exact_fp32: bool = False, split3: bool = False, scale: float = 1.0,
                timer: Optional[StageTimer] = None) -> Dict[str, torch.Tensor]:
     """mono_slam.py:100-118 for every (pair_a[i], pair_b[i]): match -> gather -> findEssentialMat(RANSAC) -> recoverPose.
     The single `focal` for both axes and recoverPose without the RANSAC mask are the reference's behaviour."""
     dev = bank.kpts.device
     pa = api._to_cuda(pair_a, torch.int32, dev)
     pb = api._to_cuda(pair_b, torch.int32, dev)
-    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer)
+    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer, split3)
     g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
     pp = (camera.cx, camera.cy)
     e = _run(timer, "essential_ransac",
@@ -116,7 +116,7 @@ def mono_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "float", ca
 
 def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary", camera: ForestCamera = ForestCamera(),
                  threshold: Optional[float] = None, ratio: Optional[float] = None, reproj_error: float = 1.0,
-                 confidence: float = 0.99, max_iters: int = 1000, exact_fp32: bool = False, scale: float = 1.0,
+                 confidence: float = 0.99, max_iters: int = 1000, exact_fp32: bool = False, split3: bool = False, scale: float = 1.0,
                  timer: Optional[StageTimer] = None) -> Dict[str, torch.Tensor]:
     """stereo_slam.py:210-306 for every pair: temporal match (left) -> gather -> depth back-projection of the previous
     frame's keypoints + joint depth filter -> solvePnPRansac (>= 6 gate) -> Rodrigues."""
@@ -125,7 +125,7 @@ def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary",
     dev = bank.kpts.device
     pa = api._to_cuda(pair_a, torch.int32, dev)
     pb = api._to_cuda(pair_b, torch.int32, dev)
-    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer)
+    m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer, split3)
     g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
     # per-correspondence disparity of the previous-left keypoint (the reference looks it up in the SGBM map)
     P, n_max = g["src_idx"].shape

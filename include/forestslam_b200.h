@@ -91,29 +91,50 @@ int fs_hamming_match(const uint8_t* desc, int n_frames, int n_max, const int32_t
  *     plus the Lowe ratio of the north star on L2 distance d = sqrt(max(0, 2 - 2 s)) of unit vectors.
  *
  * Two-step: fs_float_prepare() turns a frame bank of channel-major fp32 descriptors (SuperPoint layout
- * [256, n], superpoint.py:90-91) into the K-major split-fp16 operand bank the tensor-core kernel reads
- * (once per FRAME, not per pair); fs_float_match() then runs the tcgen05 contraction with the fused
- * row top-2 epilogue for both directions and the mutual / threshold / ratio finalisation.
+ * [256, n], superpoint.py:90-91) into the K-major split-fp16 operand bank the tensor-core kernels read
+ * (once per FRAME, not per pair); fs_float_match() then runs ONE fp16 tcgen05 pass per direction with a
+ * fused row top-3 epilogue, certifies every arg-max / threshold / ratio decision against a rigorous
+ * error bound (rescoring exactly, in fp32 on hi + lo, whatever the fp16 pass cannot prove) and applies
+ * the mutual / threshold / ratio finalisation.  Index outputs are those of the exact score.
  *
  * desc_f32   [n_frames, 256, n_max] f32   channel-major
- * operands   [n_frames, n_max, 512] fp16  (hi | lo split, x = hi + lo to 2^-25; rows >= count are zero)
- * scale      multiplies the raw dot product (superglue.py:260 uses 1/sqrt(256) = 0.0625); 1.0 = cosine
+ * operands   [n_frames, n_max + 1, 512] fp16: rows < n_max = (hi | lo) split, x = hi + lo to 2^-25, rows
+ *            >= count are zero; row n_max = per-frame norm statistics.  fs_float_operand_bytes() is its size
+ * scale      (> 0) multiplies the raw dot product (superglue.py:260 uses 1/sqrt(256) = 0.0625); 1.0 = cosine
  * threshold  keep only if scaled best score > threshold (use -inf to disable)
  * ratio      <=0: off; else keep only if d_best < ratio * d_second (float32, strict), d from raw cosine
  * outputs [n_pairs, n_max]: matches0 i32, score0 f32 (scaled best), second0 f32 (scaled runner-up,
  *   -inf when none), matches1 i32; n_matches [n_pairs].  score0/second0/matches1/n_matches may be NULL.
+ *   fs_float_match: score0 / second0 are exact wherever a decision depended on them and within the
+ *   bound (~3e-4 for unit descriptors) elsewhere; fs_float_match_split3 / _fp32 give fp32-grade values.
+ * diag       NULL or 4 x i32 on the device: [0] rows rescanned exactly, [1] rows with rescored candidates
+ * n_max      fs_float_match: <= 4096 (FS_ERR_UNSUPPORTED above; use fs_float_match_split3)
  * ---------------------------------------------------------------------------------------------- */
 #define FS_FLOAT_DIM 256
+size_t fs_float_operand_bytes(int n_frames, int n_max);
 int fs_float_prepare(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
                      void* operands_fp16, fs_stream_t stream);
-size_t fs_float_match_workspace_bytes(int n_pairs, int n_max);    /* fs_float_match_fp32 */
-size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max); /* fs_float_match */
+size_t fs_float_match_workspace_bytes(int n_pairs, int n_max);        /* fs_float_match_fp32 */
+size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max);     /* fs_float_match */
+size_t fs_float_match_split3_workspace_bytes(int n_pairs, int n_max); /* fs_float_match_split3 */
 int fs_float_match(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
                    const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
                    float scale, float threshold, float ratio,
                    int32_t* matches0, float* score0, float* second0, int32_t* matches1,
-                   int32_t* n_matches,
+                   int32_t* n_matches, int32_t* diag,
                    void* workspace, size_t workspace_bytes, fs_stream_t stream);
+/* measurement hook: only the tensor-core kernel of fs_float_match (top-3 keys into the workspace) */
+int fs_float_top3_keys(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
+                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                       void* workspace, size_t workspace_bytes, fs_stream_t stream);
+/* split-fp16 variant: three MMAs per k-step (hi.hi + lo.hi + hi.lo) give fp32-grade scores directly;
+ * row top-2 + column top-1 in one pass.  Slower; any n_max; the in-library cross-check of fs_float_match */
+int fs_float_match_split3(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
+                          const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                          float scale, float threshold, float ratio,
+                          int32_t* matches0, float* score0, float* second0, int32_t* matches1,
+                          int32_t* n_matches,
+                          void* workspace, size_t workspace_bytes, fs_stream_t stream);
 /* exact-fp32 CUDA-core variant of the same operator working directly on desc_f32 (used for n_max that
  * are not a multiple of 128 and as the in-library cross-check of the tensor-core path) */
 int fs_float_match_fp32(const float* desc_f32, int n_frames, int n_max, const int32_t* counts,
