@@ -353,7 +353,8 @@ def run_b200(args):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(cs)
             _lib.check(lib.fs_float_top3_keys(api._p(ops), int(ops.shape[0]), n_max, api._p(bank.counts), api._p(pa),
-                                              api._p(pb), P, api._p(ws), ws.numel(), api._stream()), "fs_float_top3_keys")
+                                              api._p(pb), P, int(os.environ.get("FS_TOP3_PROBE", "0")), None, api._p(ws), ws.numel(),
+                                              api._stream()), "fs_float_top3_keys")
             b.record(cs)
             spans.append((a, b))
         torch.cuda.synchronize()

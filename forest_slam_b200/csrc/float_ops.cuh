@@ -96,7 +96,7 @@ __device__ __forceinline__ float warp_dot(const OpRow8& a, const OpRow8& b) {
     return s;
 }
 
-// TMA descriptor of the operand bank: dims {512, n_max + 1, n_frames} fp16, box {64, 128, 1}, 128-byte swizzle
-int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMap* out);
+// TMA descriptor of the operand bank: dims {512, n_max + 1, n_frames} fp16, box {64, box_rows, 1}, 128-byte swizzle
+int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMap* out, int box_rows = 128);
 
 }  // namespace fs

@@ -311,7 +311,7 @@ typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuin
                                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                         CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMap* out) {
+int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMap* out, int box_rows) {
     static PFN_tmapEncodeTiled fn = nullptr;
     if (!fn) {
         void* sym = nullptr;
@@ -325,7 +325,7 @@ int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMa
     }
     const cuuint64_t gdim[3] = {512, (cuuint64_t)fs::op_rows(n_max), (cuuint64_t)n_frames};
     const cuuint64_t gstride[2] = {512 * 2, (cuuint64_t)fs::op_rows(n_max) * 512 * 2};
-    const cuuint32_t box[3] = {64, 128, 1};
+    const cuuint32_t box[3] = {64, (cuuint32_t)box_rows, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 3, const_cast<void*>(operands), gdim, gstride, box, estr,
                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,

@@ -31,10 +31,10 @@ using namespace sm100;
 
 constexpr int T3_BN = 128, T3_BK = 64, T3_KCH = FS_FLOAT_DIM / T3_BK;  // 4 k-chunks of 64
 constexpr int T3_ROWS = 256;                                          // rows per CTA (two MMA halves of 128)
-constexpr int T3_STAGES = 4;
+constexpr int T3_STAGES = 4;  // one tile; (6 stages with run-time stage indexing measured SLOWER: the MMA issue thread is the
+                              // critical path — one tile of MMAs takes as long to issue as to execute — so it gets no extra work)
 constexpr int T3_THREADS = 320;
 constexpr int T3_TMA_WARP = 8, T3_MMA_WARP = 9;  // warps 0..7 are the epilogue
-static_assert(T3_STAGES == T3_KCH, "the ring is indexed by k-chunk");
 constexpr int T3_BOX_BYTES = 128 * T3_BK * 2;               // 16 KB: one [128 x 64] fp16 box
 constexpr int T3_A_BYTES = 2 * T3_KCH * T3_BOX_BYTES;       // 128 KB
 constexpr int T3_TMEM_COLS = 512;
@@ -49,38 +49,64 @@ struct T3Barriers {
 };
 constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_BOX_BYTES + 256 /*barriers*/;
 
-// merge the sorted pair (hi >= lo) of two new keys into the running sorted triple (k1 >= k2 >= k3)
-__device__ __forceinline__ void top3_push2(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t e0, uint32_t e1) {
-    const uint32_t hi = max(e0, e1), lo = min(e0, e1);
-    const uint32_t m1 = min(k1, hi);
-    const uint32_t n3 = __vimax3_u32(k3, min(k2, hi), min(k1, lo));
-    const uint32_t n2 = __vimax3_u32(m1, k2, lo);
-    k1 = max(k1, hi);
-    k2 = n2;
-    k3 = n3;
+// (best, runner-up) of two disjoint key sets from their (best, runner-up): 3 ops
+__device__ __forceinline__ void top2_merge(uint32_t& h, uint32_t& s, uint32_t h2, uint32_t s2) {
+    s = __vimax3_u32(min(h, h2), s, s2);
+    h = max(h, h2);
 }
 
-// merge the sorted triple (t1 >= t2 >= t3) into the running sorted triple
-__device__ __forceinline__ void top3_merge3(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t t1, uint32_t t2,
-                                            uint32_t t3) {
-    const uint32_t n3 = max(__vimax3_u32(k3, t3, min(k2, t1)), min(k1, t2));
-    const uint32_t n2 = __vimax3_u32(k2, t2, min(k1, t1));
-    k1 = max(k1, t1);
-    k2 = n2;
-    k3 = n3;
+// Tournament over the 32 keys of one chunk: its best key (with column) and its runner-up key.  77 min/max ops per 32
+// columns, against 128 for a streaming top-3: the ALU pipe is what bounds this kernel's epilogue.
+__device__ __forceinline__ void chunk_top2(const uint32_t (&e)[32], uint32_t& best, uint32_t& second) {
+    uint32_t h[16], s[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) {
+        h[i] = max(e[2 * i], e[2 * i + 1]);
+        s[i] = min(e[2 * i], e[2 * i + 1]);
+    }
+#pragma unroll
+    for (int w = 8; w >= 1; w >>= 1)
+#pragma unroll
+        for (int i = 0; i < w; i++) top2_merge(h[i], s[i], h[i + w], s[i + w]);
+    best = h[0];
+    second = s[0];
 }
 
-__global__ void __launch_bounds__(T3_THREADS, 1)
-k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const void* __restrict__ operands, int n_max,
-                const int32_t* __restrict__ counts, const int32_t* __restrict__ pair_a,
-                const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0, uint32_t key_mul, uint4* __restrict__ keys) {
+// insert one key into the running sorted triple (k1 >= k2 >= k3): 5 ops
+__device__ __forceinline__ void top3_insert(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t e) {
+    const uint32_t t1 = min(k1, e);
+    k1 = max(k1, e);
+    const uint32_t t2 = min(k2, t1);
+    k2 = max(k2, t1);
+    k3 = max(k3, t2);
+}
+
+// Two CTAs that own neighbouring 256-row blocks of the same (direction, pair) form a cluster and share the streamed
+// frame: each loads HALF of every [128 x 64] box (64 rows) and multicasts it into both shared memories.  L2 -> SM traffic
+// halves (measured before: with MMAs and epilogue switched off the kernel ran at 13.7 TB/s, the L2 cap, so the real
+// kernel queued behind its own loads).  A ring stage is free when BOTH CTAs' MMAs have read it: tcgen05.commit
+// arrives on both CTAs' empty barriers (count 2).
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T3_THREADS, 1)
+k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_half,
+                const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
+                const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
+                uint32_t key_mul, int probe, long long* __restrict__ trace, uint4* __restrict__ keys) {
+#define T3_TRACE(slot)                                                                   \
+    do {                                                                                 \
+        if (trace && blockIdx.x == 0 && blockIdx.z == 0 && (int)blockIdx.y == (probe >> 8)) \
+            trace[slot] = clock64();                                                     \
+    } while (0)
+    // probe (measurement only, fs_float_top3_keys): bit 0 = issue no MMAs, bit 1 = skip the top-3 network
     // key_mul = 4096 comes in as an argument so that bits * key_mul + idx stays an IMAD (FMA pipe) instead of being
     // strength-reduced to a shift-add on the ALU pipe, which the top-3 network already saturates
+    if (threadIdx.x == 0) T3_TRACE(0);
     const int p = pair0 + blockIdx.y, dir = blockIdx.z;
     const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
     const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
     const int m0 = blockIdx.x * T3_ROWS;
-    if (m0 >= n0) return;
+    if ((int)(blockIdx.x & ~1u) * T3_ROWS >= n0) return;  // the whole cluster is past the last row
+    const bool ghost = m0 >= n0;  // no rows of its own: still loads its half of every box and frees ring stages
+    const uint32_t rank = cluster_ctarank();
     const int ntiles = (n1 + T3_BN - 1) / T3_BN;
     const int nhalf = (m0 + 128 < n0) ? 2 : 1;  // the second 128-row half may be empty
 
@@ -93,10 +119,11 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const void* __restrict
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         prefetch_tensormap(&tmap);
+        prefetch_tensormap(&tmap_half);
         mbar_init(&bar.a_full, 1);
         for (int s = 0; s < T3_STAGES; s++) {
             mbar_init(&bar.full[s], 1);
-            mbar_init(&bar.empty[s], 1);
+            mbar_init(&bar.empty[s], 2);
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(&bar.tmem_full[b], 1);
@@ -109,25 +136,30 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const void* __restrict
         tmem_relinquish();
     }
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();  // both CTAs' barriers exist before either multicasts into the other
     tc_fence_after();
     const uint32_t tmem_base = bar.tmem_base;
+    if (threadIdx.x == 0) T3_TRACE(1);
 
     if (warp == T3_TMA_WARP) {
         // ===================================================== TMA producer (one thread)
         if (lane == 0 && ntiles > 0) {
-            mbar_arrive_expect_tx(&bar.a_full, nhalf * T3_KCH * T3_BOX_BYTES);
-            for (int h = 0; h < nhalf; h++)
-                for (int kc = 0; kc < T3_KCH; kc++)
-                    tma_load_3d(sA + (h * T3_KCH + kc) * T3_BOX_BYTES, &tmap, &bar.a_full, kc * T3_BK, m0 + h * 128, fa);
-            // ring stage == k-chunk (T3_STAGES == T3_KCH): stage kc is refilled once per tile, phase = tile parity
+            if (!ghost) {
+                mbar_arrive_expect_tx(&bar.a_full, nhalf * T3_KCH * T3_BOX_BYTES);
+                for (int h = 0; h < nhalf; h++)
+                    for (int kc = 0; kc < T3_KCH; kc++)
+                        tma_load_3d(sA + (h * T3_KCH + kc) * T3_BOX_BYTES, &tmap, &bar.a_full, kc * T3_BK, m0 + h * 128, fa);
+            }
+            int it = 0;
             for (int t = 0; t < ntiles; t++) {
-#pragma unroll
-                for (int kc = 0; kc < T3_KCH; kc++) {
-                    mbar_wait(&bar.empty[kc], (t & 1) ^ 1);
-                    mbar_arrive_expect_tx(&bar.full[kc], T3_BOX_BYTES);
-                    tma_load_3d(sB + kc * T3_BOX_BYTES, &tmap, &bar.full[kc], kc * T3_BK, t * T3_BN, fb);
+                for (int kc = 0; kc < T3_KCH; kc++, it++) {
+                    const int s = it % T3_STAGES;
+                    mbar_wait(&bar.empty[s], ((it / T3_STAGES) & 1) ^ 1);
+                    mbar_arrive_expect_tx(&bar.full[s], T3_BOX_BYTES);  // own half + the peer's half
+                    tma_load_3d_multicast(sB + s * T3_BOX_BYTES + rank * (T3_BOX_BYTES / 2), &tmap_half, &bar.full[s],
+                                          kc * T3_BK, t * T3_BN + (int)rank * 64, fb, (uint16_t)3);
                 }
+                if (t < 20) T3_TRACE(10 + t);
             }
         }
     } else if (warp == T3_MMA_WARP) {
@@ -135,99 +167,108 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const void* __restrict
         // of the CTA: the sub-partition's arbiter prefers it over the two epilogue warps it shares issue slots with, so
         // the tensor pipe is never starved by the ALU-bound epilogue (measured: with the issuer as warp 1 the MMAs and
         // the epilogue of consecutive tiles ran back to back instead of overlapped).
-        if (lane == 0 && ntiles > 0) {
+        if (lane == 0 && ntiles > 0 && ghost) {
+            for (int it = 0; it < ntiles * T3_KCH; it++) {
+                const int s = it % T3_STAGES;
+                mbar_wait(&bar.full[s], (it / T3_STAGES) & 1);
+                umma_commit_multicast(&bar.empty[s], (uint16_t)3);
+            }
+        } else if (lane == 0 && ntiles > 0) {
             mbar_wait(&bar.a_full, 0);
             tc_fence_after();
+            T3_TRACE(3);
             const uint64_t a_desc0 = make_desc_k_sw128(smem_u32(sA)), b_desc0 = make_desc_k_sw128(smem_u32(sB));
+            int it = 0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_empty[buf], ((t >> 1) & 1) ^ 1);
                 tc_fence_after();
                 const uint32_t d0 = tmem_base + (buf * 2) * T3_BN;
+                if (t < 20) T3_TRACE(30 + t);
 #pragma unroll
-                for (int kc = 0; kc < T3_KCH; kc++) {
-                    mbar_wait(&bar.full[kc], t & 1);
+                for (int kc = 0; kc < T3_KCH; kc++, it++) {
+                    const int s = it % T3_STAGES;
+                    mbar_wait(&bar.full[s], (it / T3_STAGES) & 1);
                     tc_fence_after();
+                    const uint64_t bs = b_desc0 + (uint64_t)((s * T3_BOX_BYTES) >> 4);
 #pragma unroll
                     for (int ks = 0; ks < T3_BK / 16; ks++) {
                         // descriptor start-address field is in 16-byte units: +2 per K = 16 step inside the swizzle row
-                        const uint64_t bd = b_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                        const uint64_t bd = bs + (uint64_t)((ks * 32) >> 4);
                         const uint64_t ad = a_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                        if (probe & 1) continue;
                         umma_f16(d0, ad, bd, T3_IDESC, (kc | ks) != 0);
                         if (nhalf == 2)
                             umma_f16(d0 + T3_BN, ad + (uint64_t)((T3_KCH * T3_BOX_BYTES) >> 4), bd, T3_IDESC, (kc | ks) != 0);
                     }
-                    umma_commit(&bar.empty[kc]);  // ring stage free once these MMAs have read it
+                    umma_commit_multicast(&bar.empty[s], (uint16_t)3);  // ring stage read (here); the peer adds its own
                 }
                 umma_commit(&bar.tmem_full[buf]);  // both accumulators of this tile complete
+                if (t < 20) T3_TRACE(50 + t);
             }
         }
     } else {
         // ===================================================== epilogue: warps 0..7, thread = row
         const int half = warp >> 2;
         const int quarter = warp & 3;  // the TMEM lane quarter this warp may read
-        if (half < nhalf) {
+        if (half < nhalf && !ghost) {
             const int row = m0 + half * 128 + quarter * 32 + lane;
             const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
             const float sc = ps.sc;
-            uint32_t k1 = 0, k2 = 0, k3 = 0;
+            // k1 >= k2 >= k3: the three largest CHUNK maxima (each from a different 32-column chunk, column in the low
+            // bits); ks: the largest chunk runner-up.  Every column other than those of k1, k2, k3 scores <= max(k3, ks).
+            uint32_t k1 = 0, k2 = 0, k3 = 0, ks = 0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
                 tc_fence_after();
+                if (threadIdx.x == 0 && t < 20) T3_TRACE(70 + t);
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN;
-                // two register sets: the TMEM load of chunk c + 1 is in flight while chunk c goes through the network
-                uint32_t ra[32], rb[32];
-                tmem_ld_32x32b_x32(taddr, ra);
+                // the whole 128-column accumulator row goes to registers at once, and the TMEM buffer is handed back to
+                // the MMA warp BEFORE the top-3 network runs: the next-but-one tile's MMAs never wait for this warp's ALU
+                // work (measured: releasing after the last chunk's load left both pipes idle ~20 % of the time)
+                uint32_t rr[T3_BN];
+#pragma unroll
+                for (int c = 0; c < T3_BN / 32; c++) tmem_ld_32x32b_x32(taddr + c * 32, rr + c * 32);
+                tmem_ld_wait();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
+                if (probe & 2) {
+                    k1 = max(k1, rr[0] ^ rr[127]);
+                    continue;
+                }
 #pragma unroll
                 for (int c = 0; c < T3_BN / 32; c++) {
-                    uint32_t* r = (c & 1) ? rb : ra;
-                    tmem_ld_wait();
-                    if (c + 1 < T3_BN / 32) {
-                        tmem_ld_32x32b_x32(taddr + (c + 1) * 32, (c & 1) ? ra : rb);
-                    } else {  // accumulator fully read: hand it back to the MMA warp
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
-                    }
-                    // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's own top-3 is
-                    // shifted to the global column afterwards and merged into the running triple (3 + 7 ops per 32 columns)
+                    const uint32_t* r = rr + c * 32;
+                    // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is
+                    // shifted to the global column afterwards
                     const int col0 = t * T3_BN + c * 32;
                     const int nvalid = n1 - col0;
-                    uint32_t l1 = 0, l2 = 0, l3 = 0;
-                    if (nvalid >= 32) {
+                    uint32_t e[32];
 #pragma unroll
-                        for (int j = 0; j < 32; j += 2) {
-                            const uint32_t e0 = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul +
-                                                (uint32_t)(4095 - j);
-                            const uint32_t e1 = __float_as_uint(fmaf(__uint_as_float(r[j + 1]), sc, fs::KEY_BIAS)) * key_mul +
-                                                (uint32_t)(4094 - j);
-                            top3_push2(l1, l2, l3, e0, e1);
-                        }
-                    } else {
+                    for (int j = 0; j < 32; j++)
+                        e[j] = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul + (uint32_t)(4095 - j);
+                    if (nvalid < 32) {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 2) {
-                            uint32_t e0 = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul +
-                                          (uint32_t)(4095 - j);
-                            uint32_t e1 = __float_as_uint(fmaf(__uint_as_float(r[j + 1]), sc, fs::KEY_BIAS)) * key_mul +
-                                          (uint32_t)(4094 - j);
-                            e0 = (j < nvalid) ? e0 : 0u;
-                            e1 = (j + 1 < nvalid) ? e1 : 0u;
-                            top3_push2(l1, l2, l3, e0, e1);
-                        }
+                        for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
                     }
-                    // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; empty slots stay 0
-                    l1 -= l1 ? (uint32_t)col0 : 0u;
-                    l2 -= l2 ? (uint32_t)col0 : 0u;
-                    l3 -= l3 ? (uint32_t)col0 : 0u;
-                    top3_merge3(k1, k2, k3, l1, l2, l3);
+                    uint32_t cb, cs;
+                    chunk_top2(e, cb, cs);
+                    // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
+                    cb -= cb ? (uint32_t)col0 : 0u;
+                    top3_insert(k1, k2, k3, cb);
+                    ks = max(ks, cs);
                 }
+                if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
             }
-            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(k1, k2, k3, 0u);
+            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(k1, k2, k3, ks);
         }
     }
+    if (threadIdx.x == 0) T3_TRACE(4);
     tc_fence_before();
-    __syncthreads();
+    cluster_sync_all();  // the peer may still be signalling this CTA's barriers
     if (warp == T3_MMA_WARP) {
         tc_fence_after();
         tmem_dealloc(tmem_base, T3_TMEM_COLS);
@@ -263,29 +304,35 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
     const bool active = row < n0;
     const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
     const size_t o = ((size_t)dir * n_pairs_total + p) * n_max + row;
-    float v1 = -INFINITY, v2 = -INFINITY, v3 = -INFINITY;
+    float v1 = -INFINITY, v2 = -INFINITY, v3 = -INFINITY, v2s = -INFINITY;
     int i1 = 0, i2 = 0;
     bool amb_idx = false, want1 = false, want2 = false, full = false;
     if (active) {
         const uint4 k = keys[o];
         v1 = fs::key_score(k.x, ps);
         v2 = fs::key_score(k.y, ps);
-        v3 = fs::key_score(k.z, ps);
+        // k.x >= k.y >= k.z are chunk maxima, k.w the largest chunk runner-up.  Every column other than i1 and i2
+        // scores <= v3 := max(third chunk maximum, best chunk runner-up); the approximate runner-up VALUE of the row is
+        // exactly max(v2, vs) (if vs comes from another chunk than the best's, that chunk's maximum is <= k.y).
+        const float vs = fs::key_score(k.w, ps);
+        v3 = fmaxf(fs::key_score(k.z, ps), vs);
         i1 = fs::key_col(k.x);
         i2 = fs::key_col(k.y);
         const float d2 = 2.f * ps.delta;
-        amb_idx = !(v1 - v2 > d2);
+        amb_idx = !(v1 - fmaxf(v2, v3) > d2);
         const bool second_sure = (v2 - v3 > d2);  // the runner-up is certainly column i2
         if (amb_idx) {
             if (v1 - v3 > d2) want1 = want2 = true;  // the arg-max is i1 or i2
             else full = true;
         }
+        v2s = fmaxf(v2, vs);
         if (dir == 0) {
             if (isfinite(threshold) && fabsf(v1 * scale - threshold) <= ps.delta * fabsf(scale) * 1.001f + 1e-12f)
                 want1 = true;
-            if (ratio > 0.f && k.y != 0u) {
-                const bool undecided = amb_idx || (ratio_pass(v1 + ps.delta, v2 - ps.delta, ratio) !=
-                                                   ratio_pass(v1 - ps.delta, v2 + ps.delta, ratio));
+            if (ratio > 0.f && (k.y | k.w) != 0u) {
+                const float sa = fmaxf(v2, vs);
+                const bool undecided = amb_idx || (ratio_pass(v1 + ps.delta, sa - ps.delta, ratio) !=
+                                                   ratio_pass(v1 - ps.delta, sa + ps.delta, ratio));
                 if (undecided) {
                     if (second_sure) want1 = want2 = true;
                     else full = true;
@@ -315,7 +362,7 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
         }
     }
     if (!active) return;
-    float b = v1, s = v2;
+    float b = v1, s = v2s;
     int ib = i1;
     if (!full) {
         if (want1) b = ex1;
@@ -356,8 +403,19 @@ k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __
         const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)row * fs::OP_ROW_HALFS, lane);
         fs::Top2 t;
         t.init();
-        for (int c = warp; c < n1; c += 8)
-            t.push(fs::warp_dot(a, fs::load_op_row(bank_b + (size_t)c * fs::OP_ROW_HALFS, lane)), c);
+        // four columns per trip so that eight 16-byte loads per lane are in flight (one column per trip left the scan
+        // bound by one DRAM round trip per column: 325 us per launch)
+        for (int c0 = warp; c0 < n1; c0 += 32) {
+            fs::OpRow8 b[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                b[u] = fs::load_op_row(bank_b + (size_t)min(c0 + 8 * u, n1 - 1) * fs::OP_ROW_HALFS, lane);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float v = fs::warp_dot(a, b[u]);
+                if (c0 + 8 * u < n1) t.push(v, c0 + 8 * u);
+            }
+        }
         __syncthreads();  // the previous entry's merge is done with the staging arrays
         if (lane == 0) {
             s_best[warp] = t.best;
@@ -393,16 +451,17 @@ extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
 }
 
 // the tensor-core pass alone: top-3 keys of every row of both directions
-static int launch_top3(const CUtensorMap& tmap, const void* operands, int n_max, const int32_t* counts,
-                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream) {
+static int launch_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
+                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
+                       int probe = 0, long long* trace = nullptr) {
     static int granted[64];
     const int st_ = fs::ensure_dyn_smem(k_float_top3_tc, granted, (size_t)(T3_SMEM_BYTES));
     if (st_ != FS_OK) return st_;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
-        dim3 grid((n_max + T3_ROWS - 1) / T3_ROWS, np, 2);
-        k_float_top3_tc<<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs,
-                                                                     p0, 4096u, keys);
+        dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, 2);  // clusters of two along x
+        k_float_top3_tc<<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
+                                                                     p0, 4096u, probe, trace, keys);
         FS_LAUNCH_CHECK("k_float_top3_tc");
     }
     return FS_OK;
@@ -410,20 +469,21 @@ static int launch_top3(const CUtensorMap& tmap, const void* operands, int n_max,
 
 // Measurement hook (bench.py roofline): ONLY the tensor-core kernel of fs_float_match, same grid, keys into `workspace`
 extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max, const int32_t* counts,
-                                  const int32_t* pair_a, const int32_t* pair_b, int n_pairs, void* workspace,
-                                  size_t workspace_bytes, fs_stream_t stream_) {
+                                  const int32_t* pair_a, const int32_t* pair_b, int n_pairs, int probe,
+                                  long long* trace, void* workspace, size_t workspace_bytes, fs_stream_t stream_) {
     FS_REQUIRE(n_pairs > 0 && n_frames > 0 && n_max > 0 && n_max <= fs::KEY_MAX_COLS, "bad size");
     FS_REQUIRE(operands && counts && pair_a && pair_b, "null pointer");
     if (!workspace || workspace_bytes < fs_float_match_tc_workspace_bytes(n_pairs, n_max)) {
         fs::set_error("fs_float_top3_keys: workspace too small");
         return FS_ERR_WORKSPACE;
     }
-    CUtensorMap tmap;
-    const int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    CUtensorMap tmap, tmap_half;
+    int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    if (st == FS_OK) st = fs::encode_operand_map(operands, n_frames, n_max, &tmap_half, 64);
     if (st != FS_OK) return st;
     fs::Carver ws(workspace);
-    return launch_top3(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs,
-                       ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_);
+    return launch_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
+                       ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_, probe, trace);
 }
 
 extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, const int32_t* counts,
@@ -447,8 +507,9 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
         fs::set_error("fs_float_match: workspace %zu < %zu", workspace_bytes, need);
         return FS_ERR_WORKSPACE;
     }
-    CUtensorMap tmap;
+    CUtensorMap tmap, tmap_half;
     int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    if (st == FS_OK) st = fs::encode_operand_map(operands, n_frames, n_max, &tmap_half, 64);
     if (st != FS_OK) return st;
     fs::Carver ws(workspace);
     const size_t n = (size_t)n_pairs * n_max, n2 = 2 * n;
@@ -460,7 +521,7 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
     out.list = ws.take<uint32_t>(n2);
     out.counters = ws.take<int32_t>(64);
     FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));
-    st = launch_top3(tmap, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
+    st = launch_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
     if (st != FS_OK) return st;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);

@@ -123,9 +123,11 @@ int fs_float_match(const void* operands_fp16, int n_frames, int n_max, const int
                    int32_t* matches0, float* score0, float* second0, int32_t* matches1,
                    int32_t* n_matches, int32_t* diag,
                    void* workspace, size_t workspace_bytes, fs_stream_t stream);
-/* measurement hook: only the tensor-core kernel of fs_float_match (top-3 keys into the workspace) */
+/* measurement hook: only the tensor-core kernel of fs_float_match (top-3 keys into the workspace).
+ * probe = 0: the real kernel; bit 0: issue no MMAs; bit 1: skip the top-3 network (pipe-overlap experiments);
+ * trace: NULL, or 160 x i64 on the device: clock64() at the pipeline's hand-over points of the CTA of pair probe >> 8 */
 int fs_float_top3_keys(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
-                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs, int probe, long long* trace,
                        void* workspace, size_t workspace_bytes, fs_stream_t stream);
 /* split-fp16 variant: three MMAs per k-step (hi.hi + lo.hi + hi.lo) give fp32-grade scores directly;
  * row top-2 + column top-1 in one pass.  Slower; any n_max; the in-library cross-check of fs_float_match */
