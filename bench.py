@@ -495,7 +495,10 @@ def run_b200(args):
             "stats": {"mean_matches": float(res["n_matches"].float().mean()),
                       "mean_inliers": float(res["n_inliers"].float().mean()),
                       "mean_iters": float(res["iters"].float().mean()),
-                      "ok_pairs": int((res["status"] == 0).sum())}}
+                      "ok_pairs": int((res["status"] == 0).sum()),
+                      **({"matcher_rows_rescanned_exactly": int(res["match_diag"][0]),
+                          "matcher_rows_with_rescored_candidates": int(res["match_diag"][1])}
+                         if "match_diag" in res else {})}}
     if world == 1 and not args.no_cpu_baseline:
         procs = os.cpu_count() or 1
         n_s = args.cpu_sample or min(args.pairs, 8 * procs)

@@ -233,7 +233,7 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
                                                  _stream()), "fs_float_match_split3")
         else:
             ws = _workspace(lib.fs_float_match_tc_workspace_bytes(P, n_max), dev)
-            diag = torch.zeros((4,), dtype=torch.int32, device=dev) if want_diag else None
+            diag = torch.empty((4,), dtype=torch.int32, device=dev) if want_diag else None
             _lib.check(lib.fs_float_match(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
                                           rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(diag), _p(ws), ws.numel(),
                                           _stream()), "fs_float_match")

@@ -13,6 +13,13 @@
 // The same interval test guards the threshold and the ratio decisions.  Index sets are therefore those of the exact
 // score, never of the fp16 one; score values are exact where a decision depended on them and within delta elsewhere.
 //
+// Why two directions and not one pass with a column reduction: measured on B200 (256 pairs x 2048^2, this kernel's grid).
+// The two-direction form is bound by the tensor pipe (MMAs only: 0.77 ms, 105 clk per 128x128x16 = 89 % of what cuBLAS
+// sustains; epilogue only: 0.65 ms; together 0.955 ms).  A single-pass variant that also reduced every column over the
+// CTA's 256 rows (redux.sync twice per score for best + runner-up, warps merged in shared memory, row blocks in the
+// resolver) halved the MMA work but its epilogue alone took 0.93 ms (CREDUX + uniform->vector moves; a shuffle butterfly
+// needs ~5.3 ALU ops per score against 2.6 here): 1.01 ms in total, so it was dropped.
+//
 // k_float_top3_tc — one CTA = (direction, frame pair, 256-row block of the "row" frame), 320 threads:
 //   warp 8    : TMA producer.  The row block (2 x 128 rows x 256 fp16 = 128 KB) is loaded once and stays resident;
 //               the other frame streams through a 4-stage ring of [128 x 64] boxes (16 KB, 128-byte swizzle);
@@ -383,12 +390,15 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
     out.idx[o] = ib;
 }
 
-// exact top-2 over ALL columns for the rows the keys could not decide; one CTA per listed row
-__global__ void __launch_bounds__(256)
+// exact top-2 over ALL columns for the rows the keys could not decide; one CTA (16 warps) per listed row.  The scan is
+// bound by DRAM round trips (the rows are scattered over the whole bank), so every warp keeps 16 x 16-byte loads per
+// lane in flight: eight columns per trip.
+constexpr int FSCAN_WARPS = 16, FSCAN_UNROLL = 8;
+__global__ void __launch_bounds__(FSCAN_WARPS * 32)
 k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
                  const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, T3Out out) {
-    __shared__ float s_best[8], s_second[8];
-    __shared__ int s_idx[8];
+    __shared__ float s_best[FSCAN_WARPS], s_second[FSCAN_WARPS];
+    __shared__ int s_idx[FSCAN_WARPS];
     const int count = out.counters[0];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int e = blockIdx.x; e < count; e += gridDim.x) {
@@ -403,17 +413,16 @@ k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __
         const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)row * fs::OP_ROW_HALFS, lane);
         fs::Top2 t;
         t.init();
-        // four columns per trip so that eight 16-byte loads per lane are in flight (one column per trip left the scan
-        // bound by one DRAM round trip per column: 325 us per launch)
-        for (int c0 = warp; c0 < n1; c0 += 32) {
-            fs::OpRow8 b[4];
+        // columns in ascending order within the warp: c0 + FSCAN_WARPS * u
+        for (int c0 = warp; c0 < n1; c0 += FSCAN_WARPS * FSCAN_UNROLL) {
+            fs::OpRow8 b[FSCAN_UNROLL];
 #pragma unroll
-            for (int u = 0; u < 4; u++)
-                b[u] = fs::load_op_row(bank_b + (size_t)min(c0 + 8 * u, n1 - 1) * fs::OP_ROW_HALFS, lane);
+            for (int u = 0; u < FSCAN_UNROLL; u++)
+                b[u] = fs::load_op_row(bank_b + (size_t)min(c0 + FSCAN_WARPS * u, n1 - 1) * fs::OP_ROW_HALFS, lane);
 #pragma unroll
-            for (int u = 0; u < 4; u++) {
+            for (int u = 0; u < FSCAN_UNROLL; u++) {
                 const float v = fs::warp_dot(a, b[u]);
-                if (c0 + 8 * u < n1) t.push(v, c0 + 8 * u);
+                if (c0 + FSCAN_WARPS * u < n1) t.push(v, c0 + FSCAN_WARPS * u);
             }
         }
         __syncthreads();  // the previous entry's merge is done with the staging arrays
@@ -426,7 +435,7 @@ k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __
         if (threadIdx.x == 0) {
             fs::Top2 m;
             m.init();
-            for (int w = 0; w < 8; w++) m.merge(s_best[w], s_second[w], s_idx[w]);
+            for (int w = 0; w < FSCAN_WARPS; w++) m.merge(s_best[w], s_second[w], s_idx[w]);
             const size_t o = ((size_t)dir * n_pairs_total + p) * n_max + row;
             out.best[o] = m.best;
             out.second[o] = m.second;
@@ -530,7 +539,7 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
                                                    threshold, ratio, out);
         FS_LAUNCH_CHECK("k_float_resolve");
     }
-    k_float_fullscan<<<fs::sm_count() * 4, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out);
+    k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out);
     FS_LAUNCH_CHECK("k_float_fullscan");
     if (diag) FS_CUDA(cudaMemcpyAsync(diag, out.counters, 4 * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     fs::FloatRowTop2 d0{out.best, out.second, out.idx};

@@ -80,7 +80,7 @@ def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp3
             operands = _run(timer, "prepare", lambda: api.float_prepare(bank.desc_f32, bank.counts))
         r = _run(timer, "match", lambda: api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale,
                                                                threshold=threshold, ratio=ratio, operands=operands,
-                                                               exact_fp32=exact_fp32, split3=split3))
+                                                               exact_fp32=exact_fp32, split3=split3, want_diag=True))
     elif descriptor == "binary":
         if bank.desc_bin is None:
             raise ValueError("the frame bank holds no binary descriptors")
@@ -109,7 +109,8 @@ def mono_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "float", ca
     r = _run(timer, "recover_pose",
              lambda: api.recover_pose_batch(e["E"], g["mkpts0"], g["mkpts1"], g["n_corr"], focal=camera.fx, pp=pp,
                                             status=e["status"]))
-    return {"matches0": m["matches0"], "n_matches": g["n_corr"], "mkpts0": g["mkpts0"], "mkpts1": g["mkpts1"],
+    extra = {"match_diag": m["diag"]} if "diag" in m else {}
+    return {**extra, "matches0": m["matches0"], "n_matches": g["n_corr"], "mkpts0": g["mkpts0"], "mkpts1": g["mkpts1"],
             "E": e["E"], "inlier_mask": e["mask"], "n_inliers": e["n_inliers"], "status": e["status"],
             "iters": e["iters"], "R": r["R"], "t": r["t"], "pose_mask": r["mask"], "n_good": r["n_good"]}
 
