@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--exact-fp32", action="store_true", help="CUDA-core fp32 matcher instead of tcgen05")
     ap.add_argument("--split3", action="store_true", help="split-fp16 three-MMA matcher instead of the certified pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=3,
+                    help="captured pipelines (own buffers, own stream) the device loop rotates through when --overlap-steps")
     ap.add_argument("--overlap-steps", type=int, default=1,
                     help="1: consecutive steps alternate between two streams (software pipelining across steps)")
     ap.add_argument("--pos-outlier", type=float, default=-1.0,
@@ -81,7 +83,8 @@ def config_dict(args, wl, world_size):
     return {"workload": name, "kpts_per_frame": int(wl["n_kpts"]), "pairs_per_step_per_gpu": int(args.pairs),
             "image": "960x600", "gross_outlier_prob_per_observation": pos_outlier(args), "sharding": f"frame-pair index over {world_size} rank(s), one all_gather of records",
             "l2": "L2 flushed (256 MB write) between timed iterations; frame bank per step %.0f MB" % (
-                bank_bytes(args, wl) / 1e6)}
+                bank_bytes(args, wl) / 1e6),
+            "steps_in_flight": (max(2, args.lanes) if args.overlap_steps else 1)}
 
 
 def bank_bytes(args, wl):
@@ -367,14 +370,20 @@ def run_b200(args):
     # second pipeline on its own input buffers: consecutive steps alternate between the two, each on its own stream,
     # so that the latency-bound RANSAC rounds of step i run beside the tensor-core matcher of step i+1 (this is how a
     # streaming caller drives the path; the e2e loop below uses the same pair of pipelines with uploads in between)
-    devbuf2 = {k: v.clone() for k, v in devbuf.items()}
-    bank2 = seq.FrameBank(kpts=devbuf2["kpts"], counts=devbuf2["counts"], desc_f32=devbuf2.get("desc_f32"),
-                          desc_bin=devbuf2.get("desc_bin"), disparity=devbuf2.get("disparity"))
-    pipe2 = seq.CapturedPipeline(bank2, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw)
-    pipes, bufs = [pipe, pipe2], [devbuf, devbuf2]
+    n_lanes = max(2, args.lanes)
+    pipes, bufs = [pipe], [devbuf]
+    for _ in range(n_lanes - 1):
+        dbuf = {k: v.clone() for k, v in devbuf.items()}
+        bk = seq.FrameBank(kpts=dbuf["kpts"], counts=dbuf["counts"], desc_f32=dbuf.get("desc_f32"),
+                           desc_bin=dbuf.get("desc_bin"), disparity=dbuf.get("disparity"))
+        pipes.append(seq.CapturedPipeline(bk, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw))
+        bufs.append(dbuf)
     main = torch.cuda.current_stream(dev)
-    lanes = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)] if args.overlap_steps else [main, main]
-    flushes = [flush, torch.empty_like(flush)] if args.overlap_steps else [flush, flush]
+    if args.overlap_steps:
+        lanes = [torch.cuda.Stream(device=dev) for _ in range(n_lanes)]
+        flushes = [flush] + [torch.empty_like(flush) for _ in range(n_lanes - 1)]
+    else:
+        n_lanes, lanes, flushes = 1, [main], [flush]
 
     def device_loop(n_steps):
         """n_steps steps with the frame bank resident in HBM; returns (results, records) of the last step."""
@@ -382,9 +391,9 @@ def run_b200(args):
         for st_ in lanes:
             st_.wait_stream(main)
         for i in range(n_steps):
-            with torch.cuda.stream(lanes[i & 1]):
-                flushes[i & 1].zero_()  # L2 flush before every step (a 256 MB write, > 126 MB L2)
-                out = pipes[i & 1].run()
+            with torch.cuda.stream(lanes[i % n_lanes]):
+                flushes[i % n_lanes].zero_()  # L2 flush before every step (a 256 MB write, > 126 MB L2)
+                out = pipes[i % n_lanes].run()
         for st_ in lanes:
             main.wait_stream(st_)
         return out

@@ -226,3 +226,85 @@ class CapturedPipeline:
     def run(self):
         self.graph.replay()
         return self.results, self.records
+
+
+# ------------------------------------------------------------------------------------------------ loop closure (config 5)
+def triangular_index(n_frames: int, lin: torch.Tensor):
+    """Linear index of the strict upper triangle (row-major: (0,1), (0,2), ..., (0,n-1), (1,2), ...) -> (a, b), a < b."""
+    lin = lin.to(torch.int64)
+    n = int(n_frames)
+    # row a starts at s(a) = a * (2n - a - 1) / 2; invert with the quadratic formula in float64, then repair by +-1
+    a = torch.floor(((2 * n - 1) - torch.sqrt(((2 * n - 1) ** 2 - 8.0 * lin.double()).clamp(min=0))) / 2).to(torch.int64)
+    start = lambda r: r * (2 * n - r - 1) // 2
+    a = torch.where(start(a) > lin, a - 1, a)
+    a = torch.where(start(a + 1) <= lin, a + 1, a)
+    b = lin - start(a) + a + 1
+    return a, b
+
+
+def shard_all_pairs(n_frames: int, rank: int, world: int, block: int = 1024) -> torch.Tensor:
+    """Linear triangular indices owned by `rank`: blocks of `block` consecutive pairs dealt round-robin, so that every rank
+    touches every keyframe about equally."""
+    total = n_frames * (n_frames - 1) // 2
+    lin = torch.arange(total, dtype=torch.int64)
+    return lin[(lin // block) % world == rank]
+
+
+def loop_closure_pairs(bank: FrameBank, *, descriptor: str = "binary", min_matches: int = 30, rank: int = 0,
+                       world: int = 1, chunk: int = 4096, block: int = 1024, camera: ForestCamera = ForestCamera(),
+                       prob: float = 0.999, ransac_threshold: float = 1.0, max_iters: int = 1000,
+                       threshold: Optional[float] = None, scale: float = 1.0) -> torch.Tensor:
+    """All-pairs keyframe matching: every (a, b), a < b, of the bank is matched (mutual nearest neighbour); pairs with
+    more than `min_matches` mutual matches go through essential-matrix RANSAC.  This rank's share of the pairs only.
+    Returns records [n_local, 5] int64 on the device: linear pair index, a, b, n_matches, n_inliers (-1: not verified)."""
+    dev = bank.kpts.device
+    F = int(bank.kpts.shape[0])
+    lin_all = shard_all_pairs(F, rank, world, block)
+    out = torch.empty((lin_all.numel(), 5), dtype=torch.int64, device=dev)
+    operands = bank.operands
+    if descriptor == "float" and operands is None:
+        operands = api.float_prepare(bank.desc_f32, bank.counts)
+    pp = (camera.cx, camera.cy)
+    for o in range(0, lin_all.numel(), chunk):
+        lin = lin_all[o:o + chunk]
+        a, b = triangular_index(F, lin)
+        pa, pb = a.to(torch.int32).to(dev), b.to(torch.int32).to(dev)
+        if descriptor == "binary":
+            m = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, want_matches1=False)
+        else:
+            m = api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale, threshold=threshold,
+                                      operands=operands)
+        nm = m["n_matches"].to(torch.int64)
+        rec = out[o:o + lin.numel()]
+        rec[:, 0] = lin.to(dev)
+        rec[:, 1] = a.to(dev)
+        rec[:, 2] = b.to(dev)
+        rec[:, 3] = nm
+        rec[:, 4] = -1
+        sel = torch.nonzero(nm > min_matches).flatten()
+        if sel.numel():
+            g = api.gather_matches_batch(bank.kpts, bank.counts, pa[sel], pb[sel], m["matches0"][sel].contiguous())
+            e = api.find_essential_batch(g["mkpts0"], g["mkpts1"], g["n_corr"], focal=camera.fx, pp=pp, prob=prob,
+                                         threshold=ransac_threshold, max_iters=max_iters)
+            rec[sel, 4] = torch.where(e["status"] == 0, e["n_inliers"].to(torch.int64), torch.full_like(sel, -1))
+    return out
+
+
+def gather_loop_records(rec_local: torch.Tensor, n_frames: int) -> torch.Tensor:
+    """One all_gather of the loop-closure records of all ranks, restored to linear pair order."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return rec_local[torch.argsort(rec_local[:, 0])]
+    W = dist.get_world_size()
+    total = n_frames * (n_frames - 1) // 2
+    n_loc = torch.tensor([rec_local.shape[0]], dtype=torch.int64, device=rec_local.device)
+    n_max = n_loc.clone()
+    dist.all_reduce(n_max, op=dist.ReduceOp.MAX)
+    per = int(n_max.item())
+    pad = torch.full((per, rec_local.shape[1]), -1, dtype=rec_local.dtype, device=rec_local.device)
+    pad[: rec_local.shape[0]] = rec_local
+    out = torch.empty((W * per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
+    dist.all_gather_into_tensor(out, pad)
+    out = out[out[:, 0] >= 0]
+    assert out.shape[0] == total
+    return out[torch.argsort(out[:, 0])]

@@ -285,3 +285,29 @@ def test_mono_sequence_driver(fsb):
         Ti[:3, :3], Ti[:3, 3] = res["R"][p].cpu().numpy(), res["t"][p].cpu().numpy()
         acc = acc @ Ti
     assert np.abs(T[2] - acc).max() < 1e-9
+
+
+def test_loop_closure_all_pairs(fsb):
+    """Config 5 at small scale: all C(7, 2) keyframe pairs, Hamming crossCheck counts and E-RANSAC inlier counts equal
+    the literal cv2 calls pair by pair."""
+    import cv2
+    from forest_slam_b200 import sequence as seq, synth
+    world = synth.make_world(n_trunks=80, n_ground=2500, n_canopy=2500)
+    frames = synth.make_sequence(7, 700, world=world)
+    kp, dbin, df, disp, counts = synth.stack_frames(frames)
+    bank = seq.FrameBank.from_numpy(kp, counts, desc_bin=dbin)
+    rec = seq.gather_loop_records(seq.loop_closure_pairs(bank, min_matches=30, chunk=8), 7).cpu().numpy()
+    assert rec.shape == (21, 5)
+    n_verified = 0
+    for lin, a, b, nm, ni in rec:
+        fa, fb = frames[a], frames[b]
+        q, t, _ = lit.bf_hamming_match(fa.desc_bin, fb.desc_bin)
+        assert nm == q.size
+        if nm > 30:
+            E, mask = cv2.findEssentialMat(fa.kpts[q], fb.kpts[t], focal=util.FOCAL, pp=util.PP, method=cv2.RANSAC,
+                                           prob=0.999, threshold=1.0)
+            assert ni == int(mask.sum())
+            n_verified += 1
+        else:
+            assert ni == -1
+    assert n_verified >= 6
