@@ -35,10 +35,11 @@ __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1,
     for (int i = threadIdx.x; i < n; i += blockDim.x) {
         const float2 a = reinterpret_cast<const float2*>(mk0)[i];
         const float2 b = reinterpret_cast<const float2*>(mk1)[i];
-        px1[i] = ((double)a.x - ppx) / focal;
-        py1[i] = ((double)a.y - ppy) / focal;
-        px2[i] = ((double)b.x - ppx) / focal;
-        py2[i] = ((double)b.y - ppy) / focal;
+        const cvm::CvNormalise nrm(focal, ppx, ppy);
+        px1[i] = nrm.x(a.x);
+        py1[i] = nrm.y(a.y);
+        px2[i] = nrm.x(b.x);
+        py2[i] = nrm.y(b.y);
     }
 }
 
@@ -138,10 +139,11 @@ k_er_normalise(const float* __restrict__ mkpts0, const float* __restrict__ mkpts
     const float2 a = reinterpret_cast<const float2*>(mkpts0)[(size_t)p * n_max + i];
     const float2 b = reinterpret_cast<const float2*>(mkpts1)[(size_t)p * n_max + i];
     double* dst = pts + (size_t)p * 4 * n_max;
-    dst[i] = ((double)a.x - ppx) / focal;
-    dst[n_max + i] = ((double)a.y - ppy) / focal;
-    dst[2 * n_max + i] = ((double)b.x - ppx) / focal;
-    dst[3 * n_max + i] = ((double)b.y - ppy) / focal;
+    const cvm::CvNormalise nrm(focal, ppx, ppy);
+    dst[i] = nrm.x(a.x);
+    dst[n_max + i] = nrm.y(a.y);
+    dst[2 * n_max + i] = nrm.x(b.x);
+    dst[3 * n_max + i] = nrm.y(b.y);
 }
 
 __global__ void __launch_bounds__(256)

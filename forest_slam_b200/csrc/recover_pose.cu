@@ -66,8 +66,9 @@ k_rp_cheirality(const float* __restrict__ mkpts0, const float* __restrict__ mkpt
         for (int k = 0; k < 3; k++) t[k] = (combo & 2) ? -W.t[k] : W.t[k];
         const float2 pa = reinterpret_cast<const float2*>(mkpts0)[(size_t)p * n_max + i];
         const float2 pb = reinterpret_cast<const float2*>(mkpts1)[(size_t)p * n_max + i];
-        const double x1 = ((double)pa.x - ppx) / focal, y1 = ((double)pa.y - ppy) / focal;
-        const double x2 = ((double)pb.x - ppx) / focal, y2 = ((double)pb.y - ppy) / focal;
+        const cvm::CvNormalise nrm(focal, ppx, ppy);
+        const double x1 = nrm.x(pa.x), y1 = nrm.y(pa.y);
+        const double x2 = nrm.x(pb.x), y2 = nrm.y(pb.y);
         m = cvm::cheirality(R, t, x1, y1, x2, y2, dist);
     }
     const unsigned bal = __ballot_sync(0xffffffffu, m);

@@ -262,6 +262,17 @@ def sampson_error_f32(E: np.ndarray, q1: np.ndarray, q2: np.ndarray) -> np.ndarr
     return (x2tEx1 * x2tEx1 / den).astype(np.float32)
 
 
+def cv_normalise(x: np.ndarray, c: float, f: float) -> np.ndarray:
+    """cv::findEssentialMat's `points.col(k) = (points.col(k) - c) / f` as OpenCV evaluates it: the MatExpr folds the
+    division into scale = 1/f and shift = -c * (1/f), and convertTo's double kernel is a fused multiply-add.  Exact
+    rational arithmetic + one rounding = fma (pinned by tests/test_oracle_cpu.py::test_normalisation_is_fma)."""
+    from fractions import Fraction
+    a = 1.0 / f
+    b = -c * a
+    fa, fb = Fraction(a), Fraction(b)
+    return np.array([float(Fraction(float(v)) * fa + fb) for v in np.asarray(x, dtype=np.float32)], dtype=np.float64)
+
+
 def find_essential_ransac(p0: np.ndarray, p1: np.ndarray, focal: float, pp, prob: float = 0.999,
                           threshold: float = 1.0, max_iters: int = 1000, solver=None):
     """cv::findEssentialMat(RANSAC) → dict(E, mask, iters, n_inliers, trace).  `solver` may replace the
@@ -272,10 +283,10 @@ def find_essential_ransac(p0: np.ndarray, p1: np.ndarray, focal: float, pp, prob
         return None
     q1 = np.empty((n, 2))
     q2 = np.empty((n, 2))
-    q1[:, 0] = (p0[:, 0].astype(np.float64) - pp[0]) / focal
-    q1[:, 1] = (p0[:, 1].astype(np.float64) - pp[1]) / focal
-    q2[:, 0] = (p1[:, 0].astype(np.float64) - pp[0]) / focal
-    q2[:, 1] = (p1[:, 1].astype(np.float64) - pp[1]) / focal
+    q1[:, 0] = cv_normalise(p0[:, 0], pp[0], focal)
+    q1[:, 1] = cv_normalise(p0[:, 1], pp[1], focal)
+    q2[:, 0] = cv_normalise(p1[:, 0], pp[0], focal)
+    q2[:, 1] = cv_normalise(p1[:, 1], pp[1], focal)
     thr = threshold / ((focal + focal) / 2)
     thr2 = np.float32(thr * thr)
     subsets = ransac_subsets(n, max_iters) if n > 5 else np.arange(5, dtype=np.int32)[None]

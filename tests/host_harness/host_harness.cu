@@ -43,10 +43,11 @@ int hh_find_essential(const float* p0, const float* p1, int n, double focal, dou
     if (n < 5) return -1;
     std::vector<double> x1(n), y1(n), x2(n), y2(n);
     for (int i = 0; i < n; i++) {
-        x1[i] = ((double)p0[2 * i] - ppx) / focal;
-        y1[i] = ((double)p0[2 * i + 1] - ppy) / focal;
-        x2[i] = ((double)p1[2 * i] - ppx) / focal;
-        y2[i] = ((double)p1[2 * i + 1] - ppy) / focal;
+        const cvm::CvNormalise nrm(focal, ppx, ppy);
+        x1[i] = nrm.x(p0[2 * i]);
+        y1[i] = nrm.y(p0[2 * i + 1]);
+        x2[i] = nrm.x(p1[2 * i]);
+        y2[i] = nrm.y(p1[2 * i + 1]);
     }
     double thr = threshold / ((focal + focal) / 2);
     const float thr2 = (float)(thr * thr);
@@ -102,8 +103,9 @@ int hh_recover_pose(const double* E, const float* p0, const float* p1, int n, do
     int cnt[4] = {0, 0, 0, 0};
     std::vector<unsigned char> bits(n);
     for (int i = 0; i < n; i++) {
-        const double x1 = ((double)p0[2 * i] - ppx) / focal, y1 = ((double)p0[2 * i + 1] - ppy) / focal;
-        const double x2 = ((double)p1[2 * i] - ppx) / focal, y2 = ((double)p1[2 * i + 1] - ppy) / focal;
+        const cvm::CvNormalise nrm(focal, ppx, ppy);
+        const double x1 = nrm.x(p0[2 * i]), y1 = nrm.y(p0[2 * i + 1]);
+        const double x2 = nrm.x(p1[2 * i]), y2 = nrm.y(p1[2 * i + 1]);
         const bool m0 = cvm::cheirality(R1, tp, x1, y1, x2, y2, dist);
         const bool m1 = cvm::cheirality(R2, tp, x1, y1, x2, y2, dist);
         const bool m2 = cvm::cheirality(R1, tm, x1, y1, x2, y2, dist);

@@ -266,3 +266,35 @@ def test_pnp_ransac_host_code_vs_cv2_live(seed):
     ok, _, _, inl = lit.solve_pnp_ransac(P3, p2)
     c, _, mask, _ = _hh_pnp_ransac(P3, p2)
     assert ok and np.array_equal(np.nonzero(mask)[0], inl.ravel())
+
+
+def test_normalisation_is_fma():
+    """cv::findEssentialMat normalises pixels with fma(x, 1/f, -c/f) (a MatExpr folded into convertTo), not (x - c) / f.
+    tests/golden/essential_illconditioned_pair.npz is a 567-correspondence pair (synthetic frames 0 and 6 of the forest
+    sequence, Hamming crossCheck matches; mask / E from cv2 4.13 findEssentialMat) whose winning 5-subset (iteration 12)
+    is so ill-conditioned that rounding in the LAST bit of the normalised coordinates moves its inlier count:
+    cv2's own minimal solver gives 463 with the fma form (= the full cv2 call) and 459 with (x - c) / f.
+
+    KNOWN DEVIATION pinned here: our five-point restatement is not bit-identical to OpenCV's on such a subset (its
+    10x20 coefficient expansion is generated code we cannot see; candidates agree to ~1e-4 there, 1e-12 elsewhere), so
+    on THIS pair the winner has 461 inliers instead of 463.  Every other live / golden case in the suite is bit-exact."""
+    import cv2
+    g = np.load(os.path.join(util.GOLDEN, "essential_illconditioned_pair.npz"))
+    p0, p1 = g["p0"], g["p1"]
+    E, mask = cv2.findEssentialMat(p0, p1, focal=util.FOCAL, pp=util.PP, method=cv2.RANSAC, prob=0.999, threshold=1.0)
+    assert np.array_equal(mask, g["mask"]) and int(mask.sum()) == 463
+
+    def cv_solver(a, b):  # cv2's own minimal solver: findEssentialMat on exactly five points returns all candidates
+        Es = cv2.findEssentialMat(a, b, focal=1.0, pp=(0, 0), method=cv2.RANSAC, prob=0.999, threshold=1.0)[0]
+        return [] if Es is None else [Es[i:i + 3] for i in range(0, Es.shape[0], 3)]
+    r = rp.find_essential_ransac(p0, p1, util.FOCAL, util.PP, solver=cv_solver)   # fma normalisation + cv2's solver
+    assert r["n_inliers"] == 463 and np.array_equal(r["mask"], g["mask"].ravel())
+    # the formula itself, on values where the two differ
+    x = p0[:, 0]
+    q = rp.cv_normalise(x, util.PP[0], util.FOCAL)
+    naive = (x.astype(np.float64) - util.PP[0]) / util.FOCAL
+    assert np.abs(q - naive).max() < 1e-15 and np.any(q != naive)
+    # the kernel code (host build): same winning iteration, model within the documented tolerance
+    c, Eo, mo, _ = _hh_find_essential(p0, p1)
+    assert abs(c - 463) <= 2 and int((mo != g["mask"].ravel()).sum()) <= 4
+    assert np.abs(Eo - g["E"]).max() < 5e-3  # near-double root of the degree-10 polynomial: the candidate itself moves
