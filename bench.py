@@ -284,6 +284,8 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL prints its version banner on STDOUT when NCCL_DEBUG=VERSION/INFO: the bench's stdout is ONE JSON line
+        os.environ["NCCL_DEBUG"] = os.environ.get("FS_NCCL_DEBUG", "WARN")
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
 
@@ -366,6 +368,9 @@ def run_b200(args):
     # ---- the timed path: the whole step (all launches + the record gather) captured once in a CUDA graph
     kw = (dict(descriptor="float", scale=0.0625, threshold=LN_THRESH, exact_fp32=args.exact_fp32, split3=args.split3)
           if args.workload == "mono" else dict(descriptor="binary"))
+    # multi-rank: the record gather stays OUT of the graphs and is issued on one stream in step order (same order on
+    # every rank); single rank: gather_records is the identity and stays inside
+    kw["gather"] = world == 1
     pipe = seq.CapturedPipeline(bank, pa, pb, kind=args.workload, n_pairs_total=P * world, **kw)
     # second pipeline on its own input buffers: consecutive steps alternate between the two, each on its own stream,
     # so that the latency-bound RANSAC rounds of step i run beside the tensor-core matcher of step i+1 (this is how a
@@ -385,16 +390,27 @@ def run_b200(args):
     else:
         n_lanes, lanes, flushes = 1, [main], [flush]
 
+    comm = torch.cuda.Stream(device=dev)
+    gathered = [torch.cuda.Event() for _ in range(len(pipes))]
+
     def device_loop(n_steps):
         """n_steps steps with the frame bank resident in HBM; returns (results, records) of the last step."""
         out = None
-        for st_ in lanes:
+        for st_ in lanes + [comm]:
             st_.wait_stream(main)
         for i in range(n_steps):
-            with torch.cuda.stream(lanes[i % n_lanes]):
-                flushes[i % n_lanes].zero_()  # L2 flush before every step (a 256 MB write, > 126 MB L2)
-                out = pipes[i % n_lanes].run()
-        for st_ in lanes:
+            k = i % n_lanes
+            with torch.cuda.stream(lanes[k]):
+                lanes[k].wait_event(gathered[k])  # the previous gather of this pipeline's record buffer is done
+                flushes[k].zero_()  # L2 flush before every step (a 256 MB write, > 126 MB L2)
+                res_, rec_ = pipes[k].run()
+            if world > 1:
+                comm.wait_stream(lanes[k])
+                with torch.cuda.stream(comm):
+                    rec_ = seq.gather_records(rec_, P * world)  # the one collective, in step order on every rank
+                    gathered[k].record(comm)
+            out = (res_, rec_)
+        for st_ in lanes + [comm]:
             main.wait_stream(st_)
         return out
 
@@ -440,6 +456,8 @@ def run_b200(args):
             main.wait_event(copied[cur])
             flush.zero_()
             _, ar = pipes[cur].run()
+            if world > 1:
+                ar = seq.gather_records(ar, P * world)
             rec_hosts[cur].copy_(ar, non_blocking=True)
             computed[cur].record(main)
 

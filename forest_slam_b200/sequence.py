@@ -195,7 +195,10 @@ class CapturedPipeline:
     """
 
     def __init__(self, bank: FrameBank, pair_a, pair_b, kind: str = "mono", n_pairs_total: Optional[int] = None,
-                 warmup: int = 3, **kw):
+                 warmup: int = 3, gather: bool = True, **kw):
+        """gather=False keeps the collective out of the graph (records stay local): needed when several pipelines replay
+        concurrently on different streams under torch.distributed — collectives of one communicator must be issued in
+        the same order on every rank, which concurrent graph replays cannot promise."""
         if kind not in ("mono", "stereo"):
             raise ValueError("kind must be 'mono' or 'stereo'")
         dev = bank.kpts.device
@@ -210,7 +213,8 @@ class CapturedPipeline:
         def body():
             with scope:
                 res = fn(self.bank, self.pa, self.pb, **kw)
-                return res, gather_records(pack_records(res), n_total)
+                rec = pack_records(res)
+                return res, (gather_records(rec, n_total) if gather else rec)
 
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
