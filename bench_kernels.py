@@ -1,0 +1,246 @@
+#!/usr/bin/env python
+"""Per-kernel roofline table: every kernel of the path timed ALONE at a saturating batch size.
+
+Not the contract bench (that is bench.py); this answers BASELINE.json's "each choice is evidenced ... achieved HBM GB/s
+for the Hamming, scoring and triangulation kernels against B200 peak" with one JSON line per kernel:
+  {"kernel", "config", "ms", "algorithmic": {...work figures of DESIGN.md §4...}, "bound", "achieved", "peak", "frac"}
+Timing: CUDA events on the launching stream, 3 warm-ups, median of `--reps`, a 256 MB write between launches (L2 flush).
+Peaks: MEASURED_PEAKS.json (HBM, bf16 tensor) when present; CUDA-core pipe peaks are nominal figures computed from
+148 SMs x lanes x the SM clock nvidia-smi reports (stated per line).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from forest_slam_b200 import api as fsb  # noqa: E402
+from forest_slam_b200 import synth  # noqa: E402
+
+SMS = 148
+
+
+def peaks():
+    p = {"hbm_gbs": 6500.0, "tensor_tflops": 1600.0, "source": "fallback (B200_PROFILING.md)"}
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            j = json.load(open(path))
+            flat = json.dumps(j)
+            def find(d, keys):
+                for k, v in (d.items() if isinstance(d, dict) else []):
+                    if isinstance(v, (int, float)) and all(s in k.lower() for s in keys):
+                        return float(v)
+                    if isinstance(v, dict):
+                        r = find(v, keys)
+                        if r:
+                            return r
+                return None
+            h = find(j, ("hbm", "burst")) or find(j, ("hbm",)) or find(j, ("copy",))
+            t = find(j, ("bf16", "burst")) or find(j, ("bf16",)) or find(j, ("tflop",))
+            if h:
+                p["hbm_gbs"] = h
+            if t:
+                p["tensor_tflops"] = t
+            p["source"] = "measured (MEASURED_PEAKS.json)"
+            del flat
+        except Exception:
+            pass
+    return p
+
+
+def sm_clock_ghz() -> float:
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(0)
+        return pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM) / 1000.0
+    except Exception:
+        return 1.965
+
+
+class Timer:
+    def __init__(self, reps: int):
+        self.reps = reps
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def __call__(self, fn) -> float:
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(self.reps):
+            self.flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        return statistics.median(ts)
+
+
+def line(kernel, config, ms, alg, bound, achieved, peak, unit, note=""):
+    out = {"kernel": kernel, "config": config, "ms": round(ms, 5), "algorithmic": alg, "bound": bound,
+           "achieved": round(achieved, 3), "peak": round(peak, 1), "unit": unit, "frac": round(achieved / peak, 4)}
+    if note:
+        out["note"] = note
+    print(json.dumps(out), flush=True)
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=15)
+    ap.add_argument("--pairs", type=int, default=256)
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench_kernels.py needs a GPU (there is no CPU path)")
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    pk = peaks()
+    ghz = sm_clock_ghz()
+    T = Timer(args.reps)
+    P = args.pairs
+    want = set(args.only.split(",")) if args.only else None
+    g = torch.Generator(device="cpu").manual_seed(7)
+
+    def on(name):
+        return want is None or name in want
+
+    print(json.dumps({"peaks": pk, "sm_clock_ghz": ghz, "sms": SMS, "device": torch.cuda.get_device_name(0)}))
+
+    # ------------------------------------------------------------------ A2 Hamming (POPC pipe; HBM figure asked too)
+    if on("hamming"):
+        for n in (2000, 2048):
+            F = P + 1
+            desc = torch.randint(0, 256, (F, n, 32), dtype=torch.uint8, generator=g).to(dev)
+            counts = torch.full((F,), n, dtype=torch.int32, device=dev)
+            a = torch.arange(P, dtype=torch.int32, device=dev)
+            b = a + 1
+            ms = T(lambda: fsb.hamming_match_batch(desc, counts, a, b))
+            popc = P * n * n * 8.0
+            byts = P * ((n + n) * 32 + n * 12.0)
+            peak_popc = SMS * 16 * ghz  # G popc32/s at 16 lanes/clk/SM (CUDA programming guide throughput table)
+            line("k_hamming_top2 (+finalize)", {"pairs": P, "n0": n, "n1": n, "crossCheck": True}, ms,
+                 {"popc32": popc, "bytes": byts, "hbm_gbs": byts / ms / 1e6}, "popc pipe",
+                 popc / ms / 1e6, peak_popc, "Gpopc32/s",
+                 "both directions from ONE distance matrix; HBM fraction = %.4f of %.0f GB/s (operands live on chip)"
+                 % (byts / ms / 1e6 / pk["hbm_gbs"], pk["hbm_gbs"]))
+
+    # ------------------------------------------------------------------ A6 back-projection (HBM, 25 B/point)
+    if on("backproject"):
+        for npts in (1 << 20, 1 << 24):
+            pts = (torch.rand((npts, 2), generator=g) * torch.tensor([950.0, 590.0])).to(dev)
+            disp = (torch.rand((npts,), generator=g) * 60.0 + 0.5).to(dev)
+            ms = T(lambda: fsb.backproject_stereo(pts, disp))
+            byts = npts * 25.0
+            line("k_backproject", {"points": npts}, ms, {"bytes": byts}, "hbm", byts / ms / 1e6, pk["hbm_gbs"],
+                 "GB/s", "12 B in (x, y, d) + 13 B out (XYZ f32 + valid u8) per point; includes two torch.empty")
+
+    # ------------------------------------------------------------------ A1 operand preparation (HBM)
+    if on("prepare"):
+        n = 2048
+        F = P + 1
+        d = torch.randn((F, 256, n), generator=g)
+        d = (d / d.norm(dim=1, keepdim=True)).to(dev)
+        counts = torch.full((F,), n, dtype=torch.int32, device=dev)
+        ms = T(lambda: fsb.float_prepare(d, counts))
+        byts = F * n * 256 * 8.0
+        line("k_float_prepare", {"frames": F, "n": n}, ms, {"bytes": byts}, "hbm", byts / ms / 1e6, pk["hbm_gbs"],
+             "GB/s", "4 B in + 2 x 2 B out (hi | lo fp16) per descriptor component")
+        # ------------------------------------------------------------------ A1 matcher at config 2 and config 3
+        for (n, pp) in ((2048, P), (4096, 64)):
+            F = pp + 1
+            d = torch.randn((F, 256, n), generator=g)
+            d = (d / d.norm(dim=1, keepdim=True)).to(dev)
+            counts = torch.full((F,), n, dtype=torch.int32, device=dev)
+            ops = fsb.float_prepare(d, counts)
+            a = torch.arange(pp, dtype=torch.int32, device=dev)
+            b = a + 1
+            ms = T(lambda: fsb.float_match_batch(None, counts, a, b, operands=ops))
+            fl = pp * 2.0 * n * n * 256
+            line("fs_float_match (top3_tc + resolve + fullscan + finalize)", {"pairs": pp, "n": n,
+                 "descriptors": "random unit vectors (worst case for certification: no inlier margin)"}, ms,
+                 {"flop": fl}, "tensor", fl / ms / 1e9, pk["tensor_tflops"], "TFLOP/s")
+            ms3 = T(lambda: fsb.float_match_batch(None, counts, a, b, operands=ops, split3=True))
+            line("fs_float_match_split3 (k_float_match_tc)", {"pairs": pp, "n": n}, ms3, {"flop": fl}, "tensor",
+                 fl / ms3 / 1e9, pk["tensor_tflops"], "TFLOP/s", "3 MMAs per k-step (fp32-grade scores)")
+            del d, ops
+
+    # ------------------------------------------------------------------ A4 / A7 scoring sweep (config 4)
+    if on("score"):
+        K = 1200
+        cam = fsb.ForestCamera()
+        rng = np.random.default_rng(3)
+        Pn = 8
+        x0 = rng.uniform([0, 0], [960, 600], (Pn, K, 2)).astype(np.float32)
+        x1 = (x0 + rng.normal(0, 3.0, x0.shape)).astype(np.float32)
+        P3 = rng.uniform([-10, -3, 2], [10, 3, 40], (Pn, K, 3)).astype(np.float32)
+        nc = torch.full((Pn,), K, dtype=torch.int32, device=dev)
+        x0t, x1t, P3t = (torch.from_numpy(v).to(dev) for v in (x0, x1, P3))
+        fp64_peak = SMS * 64 * 2 * ghz / 1e3  # TFLOP/s: 64 DFMA lanes/clk/SM nominal (B200)
+        for H in (1024, 2048, 4096, 8192, 16384, 32768, 65536):
+            E = torch.from_numpy(rng.normal(0, 1, (Pn, H, 3, 3))).to(dev)
+            ms = T(lambda: fsb.score_essential_batch(x0t, x1t, nc, E, focal=cam.fx, pp=(cam.cx, cam.cy)))
+            ev = Pn * H * K * 1.0
+            byts = Pn * (K * 16 + H * 72 + H * 4.0)
+            line("k_score_essential", {"pairs": Pn, "H": H, "K": K}, ms,
+                 {"evals": ev, "flop": ev * 44, "bytes": byts, "hbm_gbs": byts / ms / 1e6,
+                  "gevals_per_s": ev / ms / 1e6}, "fp64 pipe", ev * 44 / ms / 1e9, fp64_peak, "TFLOP/s",
+                 "Sampson error in OpenCV's operation order, fp64, no FMA contraction (44 flop/eval)")
+            rt = torch.from_numpy(np.concatenate([rng.normal(0, 0.05, (Pn, H, 3)),
+                                                  rng.normal(0, 0.3, (Pn, H, 3))], axis=2)).to(dev)
+            ms = T(lambda: fsb.score_pnp_batch(P3t, x0t, nc, rt))
+            byts = Pn * (K * 20 + H * 48 + H * 4.0)
+            line("k_score_pnp", {"pairs": Pn, "H": H, "K": K}, ms,
+                 {"evals": ev, "flop": ev * 40, "bytes": byts, "hbm_gbs": byts / ms / 1e6,
+                  "gevals_per_s": ev / ms / 1e6}, "fp64 pipe", ev * 40 / ms / 1e9, fp64_peak, "TFLOP/s",
+                 "projectPoints with k1,k2,p1,p2,k3 in fp64 (40 flop/eval), float32 compare")
+            del E, rt
+
+    # ------------------------------------------------------------------ A3 gather (HBM)
+    if on("gather"):
+        n = 2048
+        F = P + 1
+        kp = (torch.rand((F, n, 2), generator=g) * 900).to(dev)
+        counts = torch.full((F,), n, dtype=torch.int32, device=dev)
+        a = torch.arange(P, dtype=torch.int32, device=dev)
+        b = a + 1
+        m0 = torch.randint(-1, n, (P, n), dtype=torch.int32, generator=g).to(dev)
+        ms = T(lambda: fsb.gather_matches_batch(kp, counts, a, b, m0))
+        kk = float((m0 >= 0).sum())
+        byts = P * n * 4.0 + kk * 36.0
+        line("k_gather_matches", {"pairs": P, "n": n}, ms, {"bytes": byts}, "hbm", byts / ms / 1e6, pk["hbm_gbs"],
+             "GB/s", "latency-bound at this size (a few MB per launch)")
+
+    # ------------------------------------------------------------------ SuperGlue score head (Sinkhorn, §8f rank 2)
+    if on("sinkhorn"):
+        for (m, n, pp) in ((1024, 1024, 64), (2048, 2048, 16)):
+            sc = (torch.randn((pp, m, n), generator=g) * 2.0).to(dev)
+            cm = torch.full((pp,), m, dtype=torch.int32, device=dev)
+            cn = torch.full((pp,), n, dtype=torch.int32, device=dev)
+            iters = 20
+            ms = T(lambda: fsb.sinkhorn_match_batch(sc, cm, cn, iters=iters))
+            ex2 = pp * m * n * 2.0 * iters
+            byts = pp * m * n * 4.0
+            peak_mufu = SMS * 16 * ghz  # G ex2/s at 16 MUFU lanes/clk/SM
+            line("k_sk_band x (iters + 1)", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms,
+                 {"ex2": ex2, "bytes_hbm_once": byts, "bytes_streamed": byts * (iters + 1),
+                  "stream_gbs": byts * (iters + 1) / ms / 1e6, "pairs_per_s": pp / ms * 1e3}, "mufu pipe",
+                 ex2 / ms / 1e6, peak_mufu, "Gex2/s",
+                 "2 exp per matrix element per iteration (row and column log-sum-exp); the matrix is streamed once per "
+                 "iteration, from L2 after the first (groups of pairs sized to 96 MB)")
+
+
+if __name__ == "__main__":
+    main()

@@ -249,6 +249,63 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
     return out
 
 
+# ------------------------------------------------------------------------------------------- A1' (Sinkhorn head)
+def sinkhorn_match_batch(scores: torch.Tensor, m_counts: torch.Tensor, n_counts: torch.Tensor, *,
+                         bin_score: float = 1.0, iters: int = 20, match_threshold: float = 0.2,
+                         pairs_per_group: int = 0, want_potentials: bool = False):
+    """Batched SuperGlue score head after the contraction: log_optimal_transport + mutual arg-max + exp +
+    match_threshold (superglue.py:143-172, :263-285; hyper-parameters of mono_slam.py:59-63).
+
+    scores [P, m_max, n_max] f32 on the device (n_max a multiple of 4; pair p uses its m_counts[p] x n_counts[p] block)
+    → dict(matches0, matching_scores0 [P, m_max]; matches1, matching_scores1 [P, n_max]) (+ u, v if asked)."""
+    lib = _lib.load()
+    scores = _chk(scores, torch.float32, "scores")
+    if scores.dim() != 3:
+        raise ValueError("scores must be [n_pairs, m_max, n_max]")
+    dev = scores.device
+    P, m_max, n_max = (int(x) for x in scores.shape)
+    m_counts = _chk(m_counts.to(dev), torch.int32, "m_counts")
+    n_counts = _chk(n_counts.to(dev), torch.int32, "n_counts")
+    if m_counts.numel() != P or n_counts.numel() != P:
+        raise ValueError("one (m, n) count per pair is required")
+    m0 = torch.empty((P, m_max), dtype=torch.int32, device=dev)
+    m1 = torch.empty((P, n_max), dtype=torch.int32, device=dev)
+    s0 = torch.empty((P, m_max), dtype=torch.float32, device=dev)
+    s1 = torch.empty((P, n_max), dtype=torch.float32, device=dev)
+    u = torch.zeros((P, m_max), dtype=torch.float32, device=dev) if want_potentials else None
+    v = torch.zeros((P, n_max), dtype=torch.float32, device=dev) if want_potentials else None
+    ws = _workspace(lib.fs_sinkhorn_workspace_bytes(P, m_max, n_max), dev, "sinkhorn")
+    _lib.check(lib.fs_sinkhorn_match(_p(scores), P, m_max, n_max, _p(m_counts), _p(n_counts), float(bin_score),
+                                     int(iters), float(match_threshold), int(pairs_per_group), _p(m0), _p(m1),
+                                     _p(s0), _p(s1), _p(u), _p(v), _p(ws), ws.numel(), _stream()),
+               "fs_sinkhorn_match")
+    out = {"matches0": m0, "matches1": m1, "matching_scores0": s0, "matching_scores1": s1}
+    if want_potentials:
+        out["u"], out["v"] = u, v
+    return out
+
+
+def superglue_match_head(scores, *, bin_score: float = 1.0, iters: int = 20, match_threshold: float = 0.2):
+    """One pair, host arrays in / host arrays out: the dictionary SuperGlue.forward returns (superglue.py:280-285)
+    for a [m, n] score matrix (already scaled by 1/sqrt(descriptor_dim), superglue.py:260)."""
+    dev = _dev()
+    sc = np.asarray(scores, dtype=np.float32)
+    m, n = sc.shape
+    if m == 0 or n == 0:  # superglue.py:235-242
+        return {"matches0": np.full((m,), -1, np.int64), "matches1": np.full((n,), -1, np.int64),
+                "matching_scores0": np.zeros((m,), np.float32), "matching_scores1": np.zeros((n,), np.float32)}
+    n_pad = (n + 3) // 4 * 4
+    buf = torch.zeros((1, m, n_pad), dtype=torch.float32, device=dev)
+    buf[0, :, :n] = _to_cuda(sc, torch.float32, dev)
+    cnt_m = torch.tensor([m], dtype=torch.int32, device=dev)
+    cnt_n = torch.tensor([n], dtype=torch.int32, device=dev)
+    r = sinkhorn_match_batch(buf, cnt_m, cnt_n, bin_score=bin_score, iters=iters, match_threshold=match_threshold)
+    return {"matches0": r["matches0"][0, :m].cpu().numpy().astype(np.int64),
+            "matches1": r["matches1"][0, :n].cpu().numpy().astype(np.int64),
+            "matching_scores0": r["matching_scores0"][0, :m].cpu().numpy(),
+            "matching_scores1": r["matching_scores1"][0, :n].cpu().numpy()}
+
+
 # ------------------------------------------------------------------------------------------- A3
 def gather_matches_batch(kpts: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, matches0: torch.Tensor):
     """valid = matches > -1; mkpts0 = kpts0[valid]; mkpts1 = kpts1[matches[valid]] (mono_slam.py:106-108)."""

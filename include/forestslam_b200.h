@@ -147,6 +147,28 @@ int fs_float_match_fp32(const float* desc_f32, int n_frames, int n_max, const in
                         void* workspace, size_t workspace_bytes, fs_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * A1'   SuperGlue score head after the contraction — replaces
+ *       scores = log_optimal_transport(scores, bin_score, iters)          superglue.py:143-172, :263-265
+ *       max0 / max1, mutual0 / mutual1, exp, match_threshold, -1 fill      superglue.py:268-285
+ *     with the hyper-parameters of mono_slam.py:59-63 (sinkhorn_iterations 20, match_threshold 0.2).
+ *
+ * scores     [n_pairs, m_max, n_max] f32 row-major, 16-byte aligned, n_max % 4 == 0 and <= 4096; pair p uses
+ *            its top-left m_counts[p] x n_counts[p] block (already divided by sqrt(descriptor_dim))
+ * bin_score  the dust-bin parameter alpha (superglue.py:220); iters Sinkhorn iterations
+ * pairs_per_group  <= 0: chosen so that one group's matrices stay resident in L2 over its iterations
+ * outputs    matches0 i32 / mscores0 f32 [n_pairs, m_max]; matches1 / mscores1 [n_pairs, n_max]
+ *            (-1 / 0 where unmatched, exactly the dictionary of superglue.py:280-285)
+ * u_out      NULL or [n_pairs, m_max] f32, v_out NULL or [n_pairs, n_max] f32: the dual potentials of the
+ *            ordinary rows / columns after the last iteration (for parity checks of the iteration itself)
+ * ---------------------------------------------------------------------------------------------- */
+size_t fs_sinkhorn_workspace_bytes(int n_pairs, int m_max, int n_max);
+int fs_sinkhorn_match(const float* scores, int n_pairs, int m_max, int n_max, const int32_t* m_counts,
+                      const int32_t* n_counts, float bin_score, int iters, float match_threshold,
+                      int pairs_per_group, int32_t* matches0, int32_t* matches1, float* mscores0,
+                      float* mscores1, float* u_out, float* v_out,
+                      void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------------
  * A3  match gather / order-preserving compaction — replaces
  *       valid = matches > -1 ; mkpts0 = kpts0[valid] ; mkpts1 = kpts1[matches[valid]]
  *     mono_slam.py:106-108, stereo_slam.py:216-218, :227-229 (ascending query index: this order defines

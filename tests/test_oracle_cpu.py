@@ -298,3 +298,35 @@ def test_normalisation_is_fma():
     c, Eo, mo, _ = _hh_find_essential(p0, p1)
     assert abs(c - 463) <= 2 and int((mo != g["mask"].ravel()).sum()) <= 4
     assert np.abs(Eo - g["E"]).max() < 5e-3  # near-double root of the degree-10 polynomial: the candidate itself moves
+
+
+# ---------------------------------------------------------------- SuperGlue score head
+SG = np.load(os.path.join(util.GOLDEN, "sinkhorn_golden.npz"))
+
+
+@pytest.mark.parametrize("i", range(int(SG["n_cases"])))
+def test_sinkhorn_oracle_vs_reference_golden(i):
+    """oracle/superglue_tail.py against the outputs of the reference's own log_optimal_transport + tail
+    (tests/golden/make_sinkhorn_golden.py ran superglue.py:143-172, :268-285 from /root/reference)."""
+    from oracle import superglue_tail as st
+    m, n, _, _, alpha, iters, thr = SG[f"c{i}_params"]
+    sc = SG[f"c{i}_scores"]
+    r32 = st.superglue_head(sc, float(alpha), int(iters), float(thr), np.float32)
+    r64 = st.superglue_head(sc, float(alpha), int(iters), float(thr), np.float64)
+    amb_r, amb_c = st.ambiguous_rows(r64["Z"])
+    if f"c{i}_Z" in SG.files:
+        assert np.allclose(r32["Z"], SG[f"c{i}_Z"], rtol=0, atol=2e-4)
+        assert np.allclose(r64["Z"], SG[f"c{i}_Z"], rtol=0, atol=2e-4)
+    # exact duplicates are not "ambiguous": they tie exactly and must resolve to the lowest index in both
+    assert np.array_equal(r32["matches0"], SG[f"c{i}_matches0"])
+    assert np.array_equal(r32["matches1"], SG[f"c{i}_matches1"])
+    assert np.allclose(r32["matching_scores0"], SG[f"c{i}_mscores0"], rtol=1e-3, atol=1e-6)
+    assert np.allclose(r32["matching_scores1"], SG[f"c{i}_mscores1"], rtol=1e-3, atol=1e-6)
+    # the float64 evaluation agrees wherever the decision is not a numerical tie or at the threshold's edge
+    edge = np.abs(r64["matching_scores0"] - float(thr)) < 1e-4
+    ok0 = ~amb_r & ~edge
+    sel = np.where(ok0)[0]
+    far = [k for k in sel if r64["matches0"][k] != SG[f"c{i}_matches0"][k]
+           and not (r64["matches0"][k] >= 0 and amb_c[r64["matches0"][k]])
+           and not (SG[f"c{i}_matches0"][k] >= 0 and amb_c[SG[f"c{i}_matches0"][k]])]
+    assert not far, far

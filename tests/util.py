@@ -96,6 +96,13 @@ def float_descriptors(n0, n1, seed, shared=0.6, sigma=0.05):
     return obs(n0), obs(n1)
 
 
+def sinkhorn_scores(m, n, seed, gain=20.0, shared=0.6):
+    """A SuperGlue-like score matrix [m, n] f32: gain * cosine of noisy shared descriptors (the reference's scores are
+    dot products of unnormalised 256-d projections divided by 16, superglue.py:259-260: O(10) for matches, O(1) else)."""
+    d0, d1 = float_descriptors(m, n, seed, shared=shared)
+    return np.ascontiguousarray((gain * (d0.T.astype(np.float64) @ d1.astype(np.float64))).astype(np.float32))
+
+
 _hh = None
 
 
