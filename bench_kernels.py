@@ -234,12 +234,18 @@ def main():
             ex2 = pp * m * n * 2.0 * iters
             byts = pp * m * n * 4.0
             peak_mufu = SMS * 16 * ghz  # G ex2/s at 16 MUFU lanes/clk/SM
-            line("k_sk_band x (iters + 1)", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms,
+            line("k_sk_resident (cooperative, 1 launch per group)", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms,
                  {"ex2": ex2, "bytes_hbm_once": byts, "bytes_streamed": byts * (iters + 1),
                   "stream_gbs": byts * (iters + 1) / ms / 1e6, "pairs_per_s": pp / ms * 1e3}, "mufu pipe",
                  ex2 / ms / 1e6, peak_mufu, "Gex2/s",
-                 "2 exp per matrix element per iteration (row and column log-sum-exp); the matrix is streamed once per "
-                 "iteration, from L2 after the first (groups of pairs sized to 96 MB)")
+                 "2 exp per matrix element per iteration (row and column log-sum-exp); "
+                 "resident kernel: the matrix is read from HBM once and stays in shared memory for all "
+                 "iterations; two pair-wide barriers per iteration")
+            ms_s = T(lambda: fsb.sinkhorn_match_batch(sc, cm, cn, iters=iters, pairs_per_group=-1))
+            line("k_sk_band x (iters + 1) [streaming variant]", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms_s,
+                 {"ex2": ex2, "bytes_streamed": byts * (iters + 1), "stream_gbs": byts * (iters + 1) / ms_s / 1e6,
+                  "pairs_per_s": pp / ms_s * 1e3}, "mufu pipe", ex2 / ms_s / 1e6, peak_mufu, "Gex2/s",
+                 "one launch per iteration, matrices streamed from L2 (groups of pairs sized to 96 MB)")
 
 
 if __name__ == "__main__":

@@ -45,6 +45,7 @@ SIGNATURES = {
                                         C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_match_fp32": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,
                                       C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
+    "fs_float_scores": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, ptr, ptr]),
     "fs_sinkhorn_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "fs_sinkhorn_match": (C.c_int, [ptr, C.c_int, C.c_int, C.c_int, ptr, ptr, C.c_float, C.c_int, C.c_float,
                                     C.c_int, ptr, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),

@@ -285,6 +285,42 @@ def sinkhorn_match_batch(scores: torch.Tensor, m_counts: torch.Tensor, n_counts:
     return out
 
 
+def float_scores_batch(counts: torch.Tensor, pair_a, pair_b, *, operands: torch.Tensor, scale: float = 0.0625):
+    """scores[p] = scale * desc_a^T desc_b (superglue.py:259-260; scale = 1/sqrt(256)) on the tensor cores →
+    [P, n_max, n_max] f32 on the device (rows / columns beyond the frames' counts carry no information)."""
+    lib = _lib.load()
+    operands = _chk(operands, torch.float16, "operands")
+    dev = operands.device
+    F, n_max = int(operands.shape[0]), int(operands.shape[1]) - 1
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    a, b = _pairs(pair_a, pair_b, dev)
+    P = int(a.numel())
+    out = torch.empty((P, n_max, n_max), dtype=torch.float32, device=dev)
+    _lib.check(lib.fs_float_scores(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), _p(out),
+                                   _stream()), "fs_float_scores")
+    return out
+
+
+def superglue_head_batch(desc: Optional[torch.Tensor], counts: torch.Tensor, pair_a, pair_b, *,
+                         operands: Optional[torch.Tensor] = None, scale: float = 0.0625, bin_score: float = 1.0,
+                         iters: int = 20, match_threshold: float = 0.2):
+    """The whole tail of SuperGlue.forward after final_proj (superglue.py:259-285) for a batch of frame pairs:
+    contraction / sqrt(d) on the tensor cores → log-Sinkhorn with dust-bins → mutual arg-max, exp, threshold.
+    desc [F, 256, n_max] f32 (n_max a multiple of 128) or the prepared operand bank."""
+    if operands is None:
+        if desc is None:
+            raise ValueError("either desc or operands is required")
+        operands = float_prepare(_chk(desc, torch.float32, "desc"), counts)
+    dev = operands.device
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    a, b = _pairs(pair_a, pair_b, dev)
+    scores = float_scores_batch(counts, a, b, operands=operands, scale=scale)
+    r = sinkhorn_match_batch(scores, counts[a.long()].contiguous(), counts[b.long()].contiguous(),
+                             bin_score=bin_score, iters=iters, match_threshold=match_threshold)
+    r["scores"] = scores
+    return r
+
+
 def superglue_match_head(scores, *, bin_score: float = 1.0, iters: int = 20, match_threshold: float = 0.2):
     """One pair, host arrays in / host arrays out: the dictionary SuperGlue.forward returns (superglue.py:280-285)
     for a [m, n] score matrix (already scaled by 1/sqrt(descriptor_dim), superglue.py:260)."""

@@ -124,11 +124,14 @@ __device__ __forceinline__ uint32_t f2ord(float v) {
     return b ^ ((uint32_t)((int32_t)b >> 31) | 0x80000000u);
 }
 
+// STORE = true: the same contraction with a plain epilogue that writes scale * score to scores_out [P, n_max, n_max]
+// (fs_float_scores: the score matrix log_optimal_transport consumes, superglue.py:259-260).
+template <bool STORE>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int32_t* __restrict__ counts,
                  const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b,
                  float* __restrict__ row_best, float* __restrict__ row_second, int32_t* __restrict__ row_idx,
-                 unsigned long long* __restrict__ col_best) {
+                 unsigned long long* __restrict__ col_best, float* __restrict__ scores_out, float scale) {
     const int p = blockIdx.y;
     const int fa = pair_a[p], fb = pair_b[p];
     const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
@@ -241,6 +244,19 @@ k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int3
                     if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
                 }
                 const int col0 = t * TC_BN + c * 32;
+                if constexpr (STORE) {
+                    // thread = row: 32 consecutive columns = one full 128-byte line per thread.  Columns >= n1 are
+                    // products with zero operand rows (stored as 0, never read by the consumer).
+                    if (row_ok) {
+                        float4* dst = reinterpret_cast<float4*>(scores_out + ((size_t)p * n_max + row) * n_max + col0);
+#pragma unroll
+                        for (int j = 0; j < 8; j++)
+                            __stcs(dst + j, make_float4(__uint_as_float(r[4 * j]) * scale, __uint_as_float(r[4 * j + 1]) * scale,
+                                                        __uint_as_float(r[4 * j + 2]) * scale,
+                                                        __uint_as_float(r[4 * j + 3]) * scale));
+                    }
+                    continue;
+                }
                 const int nvalid = n1 - col0;  // columns of this chunk that exist
                 uint32_t mykey = 0;
 #pragma unroll
@@ -259,6 +275,7 @@ k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int3
                 }
                 part[c * 32 + lane] = mykey;
             }
+            if constexpr (STORE) continue;
             named_bar_sync(1, 128);
             {
                 // merge the four warps' partials of column `etid`, one 64-bit atomicMax per (column, CTA)
@@ -280,7 +297,7 @@ k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int3
                 }
             }
         }
-        if (row_ok) {
+        if (!STORE && row_ok) {
             const size_t o = (size_t)p * n_max + row;
             row_best[o] = best;
             row_second[o] = second;
@@ -385,20 +402,50 @@ extern "C" int fs_float_match_split3(const void* operands, int n_frames, int n_m
     FS_CUDA(cudaMemsetAsync(col_best, 0, n * sizeof(unsigned long long), stream));
     {
         static int granted[64];
-        const int st_ = fs::ensure_dyn_smem(k_float_match_tc, granted, (size_t)(TC_SMEM_BYTES));
+        const int st_ = fs::ensure_dyn_smem(k_float_match_tc<false>, granted, (size_t)(TC_SMEM_BYTES));
         if (st_ != FS_OK) return st_;
     }
     for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
         const int np = min(65535, n_pairs - p0);
         const size_t o = (size_t)p0 * n_max;
         dim3 grid((n_max + TC_BM - 1) / TC_BM, np);
-        k_float_match_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(tmap, n_max, counts, pair_a + p0, pair_b + p0,
-                                                                      d0.best + o, d0.second + o, d0.idx + o,
-                                                                      col_best + o);
+        k_float_match_tc<false><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(
+            tmap, n_max, counts, pair_a + p0, pair_b + p0, d0.best + o, d0.second + o, d0.idx + o, col_best + o,
+            nullptr, 1.f);
         FS_LAUNCH_CHECK("k_float_match_tc");
     }
     k_unpack_cols<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(col_best, n, idx1);
     FS_LAUNCH_CHECK("k_unpack_cols");
     return fs::launch_float_finalize(n_max, counts, pair_a, pair_b, n_pairs, d0, idx1, scale, threshold, ratio, matches0,
                                      score0, second0, matches1, n_matches, stream);
+}
+
+// Score matrices for the SuperGlue head: scores[p, i, j] = scale * <d_a[i], d_b[j]> (superglue.py:259-260), fp32-grade
+// (split-fp16, three MMAs per k-step), written once to HBM for fs_sinkhorn_match.
+extern "C" int fs_float_scores(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                               const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float* scores,
+                               fs_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    FS_REQUIRE(n_pairs >= 0 && n_frames >= 0 && n_max >= 0, "negative size");
+    if (n_pairs == 0 || n_max == 0) return FS_OK;
+    FS_REQUIRE(operands && counts && pair_a && pair_b && scores, "null pointer");
+    FS_REQUIRE(n_max % TC_BN == 0, "n_max must be a multiple of 128");
+    FS_REQUIRE(((uintptr_t)operands & 15) == 0 && ((uintptr_t)scores & 15) == 0, "buffers must be 16-byte aligned");
+    CUtensorMap tmap;
+    int st = fs::encode_operand_map(operands, n_frames, n_max, &tmap);
+    if (st != FS_OK) return st;
+    {
+        static int granted[64];
+        const int st_ = fs::ensure_dyn_smem(k_float_match_tc<true>, granted, (size_t)(TC_SMEM_BYTES));
+        if (st_ != FS_OK) return st_;
+    }
+    for (int p0 = 0; p0 < n_pairs; p0 += 65535) {
+        const int np = min(65535, n_pairs - p0);
+        dim3 grid((n_max + TC_BM - 1) / TC_BM, np);
+        k_float_match_tc<true><<<grid, TC_THREADS, TC_SMEM_BYTES, stream>>>(
+            tmap, n_max, counts, pair_a + p0, pair_b + p0, nullptr, nullptr, nullptr, nullptr,
+            scores + (size_t)p0 * n_max * n_max, scale);
+        FS_LAUNCH_CHECK("k_float_match_tc<store>");
+    }
+    return FS_OK;
 }

@@ -155,12 +155,21 @@ int fs_float_match_fp32(const float* desc_f32, int n_frames, int n_max, const in
  * scores     [n_pairs, m_max, n_max] f32 row-major, 16-byte aligned, n_max % 4 == 0 and <= 4096; pair p uses
  *            its top-left m_counts[p] x n_counts[p] block (already divided by sqrt(descriptor_dim))
  * bin_score  the dust-bin parameter alpha (superglue.py:220); iters Sinkhorn iterations
- * pairs_per_group  <= 0: chosen so that one group's matrices stay resident in L2 over its iterations
+ * pairs_per_group  0: as many pairs per cooperative launch as are co-resident in shared memory (the matrix is read
+ *            from HBM once and stays on chip for all iterations); > 0: an upper limit; < 0: force the streaming
+ *            variant (one launch per iteration, matrices kept in L2) that is otherwise only used when a single
+ *            pair's bands exceed the co-resident capacity (measurement / test hook)
  * outputs    matches0 i32 / mscores0 f32 [n_pairs, m_max]; matches1 / mscores1 [n_pairs, n_max]
  *            (-1 / 0 where unmatched, exactly the dictionary of superglue.py:280-285)
  * u_out      NULL or [n_pairs, m_max] f32, v_out NULL or [n_pairs, n_max] f32: the dual potentials of the
  *            ordinary rows / columns after the last iteration (for parity checks of the iteration itself)
  * ---------------------------------------------------------------------------------------------- */
+/* scores[p, i, j] = scale * <desc_a[i], desc_b[j]> on the tensor cores (split-fp16, fp32-grade), the matrix
+ * superglue.py:259-260 hands to log_optimal_transport: [n_pairs, n_max, n_max] f32, n_max % 128 == 0; rows >= the
+ * count of frame a are not written, columns >= the count of frame b are 0 */
+int fs_float_scores(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
+                    const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float* scores,
+                    fs_stream_t stream);
 size_t fs_sinkhorn_workspace_bytes(int n_pairs, int m_max, int n_max);
 int fs_sinkhorn_match(const float* scores, int n_pairs, int m_max, int n_max, const int32_t* m_counts,
                       const int32_t* n_counts, float bin_score, int iters, float match_threshold,

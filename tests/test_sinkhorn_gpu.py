@@ -130,3 +130,55 @@ def test_sinkhorn_group_size_invariance(fsb):
     b = fsb.sinkhorn_match_batch(buf, cm, cn, want_potentials=True, pairs_per_group=1)
     for k in ("matches0", "matches1", "matching_scores0", "u", "v"):
         assert torch.equal(a[k], b[k]), k
+
+
+def test_sinkhorn_streaming_variant_agrees(fsb):
+    """The per-iteration (L2-streaming) fallback and the shared-memory-resident kernel compute the same thing."""
+    import torch
+    P, m, n = 3, 333, 512
+    buf = torch.from_numpy(np.stack([util.sinkhorn_scores(m, n, 950 + p) for p in range(P)])).cuda()
+    cm = torch.tensor([m, 17, 200], dtype=torch.int32)
+    cn = torch.tensor([n, 512, 3], dtype=torch.int32)
+    a = fsb.sinkhorn_match_batch(buf, cm, cn, want_potentials=True)
+    b = fsb.sinkhorn_match_batch(buf, cm, cn, want_potentials=True, pairs_per_group=-1)
+    torch.cuda.synchronize()
+    assert (a["u"] - b["u"]).abs().max().item() < 1e-4 and (a["v"] - b["v"]).abs().max().item() < 1e-4
+    assert (a["matches0"] != b["matches0"]).float().mean().item() < 0.01
+    assert torch.allclose(a["matching_scores0"], b["matching_scores0"], rtol=1e-3, atol=1e-6) or \
+        ((a["matching_scores0"] > 0) != (b["matching_scores0"] > 0)).float().mean().item() < 0.01
+
+
+def test_superglue_head_from_descriptors(fsb):
+    """Contraction on the tensor cores (fs_float_scores) + Sinkhorn head against the oracle fed with the float64
+    score matrix: scores to 2e-6 absolute (fp32-grade), then the usual head bars."""
+    import torch
+    n_max, F = 512, 4
+    counts = [512, 400, 130, 0]
+    bank = np.zeros((F, 256, n_max), np.float32)
+    for f in range(F - 1):
+        d0, _ = util.float_descriptors(counts[f], 8, 40 + f)
+        bank[f, :, :counts[f]] = d0
+    # frames 0 and 1 observe shared landmarks
+    d0, d1 = util.float_descriptors(counts[0], counts[1], 77)
+    bank[0, :, :counts[0]], bank[1, :, :counts[1]] = d0, d1
+    dev = torch.device("cuda:0")
+    gain = 20.0  # scores of matched pairs near 20 * cos, like tests.util.sinkhorn_scores
+    r = fsb.superglue_head_batch(torch.from_numpy(bank).to(dev), torch.tensor(counts, dtype=torch.int32),
+                                 [0, 1, 2, 0], [1, 2, 0, 3], scale=gain)
+    torch.cuda.synchronize()
+    for p, (a, b) in enumerate([(0, 1), (1, 2), (2, 0), (0, 3)]):
+        m, n = counts[a], counts[b]
+        g0 = r["matches0"][p].cpu().numpy()
+        g1 = r["matches1"][p].cpu().numpy()
+        if m == 0 or n == 0:
+            assert (g0 == -1).all() and (g1 == -1).all()
+            continue
+        ref_sc = (gain * (bank[a, :, :m].T.astype(np.float64) @ bank[b, :, :n].astype(np.float64)))
+        got_sc = r["scores"][p, :m, :n].cpu().numpy()
+        assert np.abs(got_sc - ref_sc).max() < 2e-6 * gain, np.abs(got_sc - ref_sc).max()
+        r64 = st.superglue_head(ref_sc, 1.0, 20, 0.2, np.float64)
+        r32 = st.superglue_head(ref_sc.astype(np.float32), 1.0, 20, 0.2, np.float32)
+        _check_indices(g0[:m], g1[:n], r32["matches0"], r32["matches1"], r64, 0.2)
+        assert (g0[m:] == -1).all() and (g1[n:] == -1).all()
+        if (a, b) == (0, 1):
+            assert (g0[:m] >= 0).sum() > 100
