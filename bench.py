@@ -223,7 +223,8 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------ B200 arm
 # stage of the step -> the kernel that is (all but a few microseconds of) it; ncu launch lists under profiles/ use
 # these names
-STAGE_KERNEL = {"match": {"mono": "k_float_top3_tc", "stereo": "k_hamming_top2"}, "prepare": "k_float_prepare",
+STAGE_KERNEL = {"match": {"mono": "k_float_top3_tc", "stereo": "k_float_top3_tc (+-1 Hamming operands)"},
+                "prepare": {"mono": "k_float_prepare", "stereo": "k_hamming_expand"},
                 "gather": "k_gather_matches", "essential_ransac": "k_rg_select/solve/tail/score<EPolicy> rounds",
                 "recover_pose": "k_rp_cheirality", "triangulate": "k_backproject_filter",
                 "pnp_ransac": "k_rg_select/solve/score<PPolicy> rounds + k_pnp_refine"}
@@ -256,6 +257,8 @@ def stage_work(args, wl, res, stage: str):
     it = float(res["iters"].float().mean().item()) if "iters" in res else 0.0
     if stage == "match" and args.workload == "mono":
         return "tensor", P * 2.0 * n * n * 256, "TFLOP/s"
+    if stage == "prepare" and args.workload != "mono":
+        return "hbm", (P + 1) * n * (32.0 + 1024.0), "GB/s"  # 32 B of bits in, one 1 KB fp16 operand row out, per descriptor
     if stage == "prepare":
         return "hbm", (P + 1) * n * 256 * (4.0 + 4.0), "GB/s"  # fp32 in, fp16 hi + lo out, once per frame
     if stage == "match":

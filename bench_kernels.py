@@ -127,7 +127,7 @@ def main():
             counts = torch.full((F,), n, dtype=torch.int32, device=dev)
             a = torch.arange(P, dtype=torch.int32, device=dev)
             b = a + 1
-            ms = T(lambda: fsb.hamming_match_batch(desc, counts, a, b))
+            ms = T(lambda: fsb.hamming_match_batch(desc, counts, a, b, popc=True))
             popc = P * n * n * 8.0
             byts = P * ((n + n) * 32 + n * 12.0)
             peak_popc = SMS * 16 * ghz  # G popc32/s at 16 lanes/clk/SM (CUDA programming guide throughput table)
@@ -136,6 +136,18 @@ def main():
                  popc / ms / 1e6, peak_popc, "Gpopc32/s",
                  "both directions from ONE distance matrix; HBM fraction = %.4f of %.0f GB/s (operands live on chip)"
                  % (byts / ms / 1e6 / pk["hbm_gbs"], pk["hbm_gbs"]))
+
+            # tensor-core variant: the same N0 x N1 x 256 bit comparisons as a +-1 fp16 contraction (hamming_tc.cu)
+            ops = fsb.hamming_prepare(desc, counts)
+            ms_p = T(lambda: fsb.hamming_prepare(desc, counts))
+            ms_t = T(lambda: fsb.hamming_match_batch(None, counts, a, b, operands=ops))
+            flop = P * 2.0 * n * n * 256
+            line("fs_hamming_match_tc (k_float_top3_tc on +-1 operands + finalize)",
+                 {"pairs": P, "n0": n, "n1": n, "crossCheck": True}, ms_t,
+                 {"flop": flop, "popc32_equivalent": popc, "equiv_gpopc32_per_s": popc / ms_t / 1e6,
+                  "speedup_vs_popc_kernel": ms / ms_t, "prepare_ms_per_%d_frames" % F: ms_p},
+                 "tensor", flop / ms_t / 1e9, pk["tensor_tflops"], "TFLOP/s",
+                 "one fp16 tcgen05 pass per direction (2x the algorithmic MMA work, roofline counts 1x); exact integers")
 
     # ------------------------------------------------------------------ A6 back-projection (HBM, 25 B/point)
     if on("backproject"):

@@ -33,6 +33,11 @@ SIGNATURES = {
     "fs_hamming_match_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fs_hamming_match": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_int, C.c_float,
                                    ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
+    "fs_hamming_operand_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "fs_hamming_prepare": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr]),
+    "fs_hamming_match_tc_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "fs_hamming_match_tc": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_int, C.c_float,
+                                      ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_prepare": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr]),
     "fs_float_match_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fs_float_match_tc_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),

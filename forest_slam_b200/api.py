@@ -140,17 +140,45 @@ def _pairs(pair_a, pair_b, device):
 
 
 # ------------------------------------------------------------------------------------------- A2
-def hamming_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, *, cross_check: bool = True,
-                        ratio: Optional[float] = None, want_matches1: bool = True):
-    """Batched cv2.BFMatcher(NORM_HAMMING, crossCheck).match over a frame bank (stereo_slam.py:85,234,242).
+HAMMING_TC_MAX_COLS = 4096  # fs_hamming_match_tc packs the column index into 12 key bits
 
-    desc [F, n_max, 32] uint8, counts [F] int32 → dict(matches0, dist0, second0, matches1, n_matches)."""
+
+def hamming_prepare(desc: torch.Tensor, counts: torch.Tensor) -> torch.Tensor:
+    """[F, n_max, 32] uint8 ORB rows → [F, n_max + 1, 512] fp16 operand bank of the tensor-core Hamming matcher
+    (every bit a +-1 operand: dot = 256 - 2 * hamming, exact).  Once per FRAME; any number of pairs reuse it."""
     lib = _lib.load()
     desc = _chk(desc, torch.uint8, "desc")
     if desc.dim() != 3 or desc.shape[2] != 32:
         raise ValueError("desc must be [n_frames, n_max, 32] uint8")
     dev = desc.device
     F, n_max = int(desc.shape[0]), int(desc.shape[1])
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    ops = torch.empty((F, n_max + 1, 512), dtype=torch.float16, device=dev)
+    assert ops.numel() * 2 == lib.fs_hamming_operand_bytes(F, n_max) or F == 0 or n_max == 0
+    _lib.check(lib.fs_hamming_prepare(_p(desc), F, n_max, _p(counts), _p(ops), _stream()), "fs_hamming_prepare")
+    return ops
+
+
+def hamming_match_batch(desc: Optional[torch.Tensor], counts: torch.Tensor, pair_a, pair_b, *,
+                        cross_check: bool = True, ratio: Optional[float] = None, want_matches1: bool = True,
+                        operands: Optional[torch.Tensor] = None, popc: bool = False):
+    """Batched cv2.BFMatcher(NORM_HAMMING, crossCheck).match over a frame bank (stereo_slam.py:85,234,242).
+
+    desc [F, n_max, 32] uint8, counts [F] int32 → dict(matches0, dist0, second0, matches1, n_matches).
+    Default: the tensor-core kernel (hamming_tc.cu) on ``operands`` from hamming_prepare (prepared on the fly when
+    absent); ``popc=True`` or n_max > 4096 selects the POPC-pipe kernel (hamming.cu).  Both give the same bits."""
+    lib = _lib.load()
+    if desc is not None:
+        desc = _chk(desc, torch.uint8, "desc")
+        if desc.dim() != 3 or desc.shape[2] != 32:
+            raise ValueError("desc must be [n_frames, n_max, 32] uint8")
+        dev = desc.device
+        F, n_max = int(desc.shape[0]), int(desc.shape[1])
+    else:
+        if operands is None:
+            raise ValueError("either desc or operands is required")
+        dev = operands.device
+        F, n_max = int(operands.shape[0]), int(operands.shape[1]) - 1
     counts = _chk(counts.to(dev), torch.int32, "counts")
     a, b = _pairs(pair_a, pair_b, dev)
     P = int(a.numel())
@@ -159,12 +187,28 @@ def hamming_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b
     s0 = torch.empty_like(m0)
     m1 = torch.empty_like(m0) if want_matches1 else None
     nm = torch.empty((P,), dtype=torch.int32, device=dev)
+    out = {"matches0": m0, "dist0": d0, "second0": s0, "matches1": m1, "n_matches": nm}
+    use_tc = TENSOR_CORE_MATCHER and not popc and n_max <= HAMMING_TC_MAX_COLS
+    if use_tc:
+        if operands is None:
+            operands = hamming_prepare(desc, counts)
+        operands = _chk(operands, torch.float16, "operands")
+        if tuple(operands.shape) != (F, n_max + 1, 512):
+            raise ValueError("operands must be the [n_frames, n_max + 1, 512] fp16 bank hamming_prepare returns")
+        ws = _workspace(lib.fs_hamming_match_tc_workspace_bytes(P, n_max), dev)
+        _lib.check(lib.fs_hamming_match_tc(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P,
+                                           int(bool(cross_check)), float(ratio) if ratio else 0.0, _p(m0), _p(d0),
+                                           _p(s0), _p(m1), _p(nm), _p(ws), ws.numel(), _stream()),
+                   "fs_hamming_match_tc")
+        return out
+    if desc is None:
+        raise ValueError("the POPC kernel needs desc")
     nbytes = lib.fs_hamming_match_workspace_bytes(P, n_max)
     ws = _workspace(nbytes, dev)
     _lib.check(lib.fs_hamming_match(_p(desc), F, n_max, _p(counts), _p(a), _p(b), P, int(bool(cross_check)),
                                     float(ratio) if ratio else 0.0, _p(m0), _p(d0), _p(s0), _p(m1), _p(nm),
                                     _p(ws), ws.numel(), _stream()), "fs_hamming_match")
-    return {"matches0": m0, "dist0": d0, "second0": s0, "matches1": m1, "n_matches": nm}
+    return out
 
 
 # ------------------------------------------------------------------------------------------- A1

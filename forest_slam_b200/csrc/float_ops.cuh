@@ -99,4 +99,10 @@ __device__ __forceinline__ float warp_dot(const OpRow8& a, const OpRow8& b) {
 // TMA descriptor of the operand bank: dims {512, n_max + 1, n_frames} fp16, box {64, box_rows, 1}, 128-byte swizzle
 int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMap* out, int box_rows = 128);
 
+// k_float_top3_tc (float_top3.cu) over both directions of every pair: keys [2][n_pairs][n_max] uint4 =
+// (three largest 32-column-chunk maxima, largest chunk runner-up), each key = score bits << 12 | (4095 - column)
+int launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max,
+                      const int32_t* counts, const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys,
+                      cudaStream_t stream, int probe = 0, long long* trace = nullptr);
+
 }  // namespace fs

@@ -459,10 +459,11 @@ extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
     return fs::align_up(n2 * 16, 256) + 4 * fs::align_up(n2 * 4, 256) + 256 + 256;
 }
 
-// the tensor-core pass alone: top-3 keys of every row of both directions
-static int launch_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
-                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
-                       int probe = 0, long long* trace = nullptr) {
+// the tensor-core pass alone: top-3 keys of every row of both directions (also the first stage of the tensor-core
+// Hamming matcher, hamming_tc.cu: +-1 operands make the same kernel an exact integer scorer)
+int fs::launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
+                          const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
+                          int probe, long long* trace) {
     static int granted[64];
     const int st_ = fs::ensure_dyn_smem(k_float_top3_tc, granted, (size_t)(T3_SMEM_BYTES));
     if (st_ != FS_OK) return st_;
@@ -491,7 +492,7 @@ extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max,
     if (st == FS_OK) st = fs::encode_operand_map(operands, n_frames, n_max, &tmap_half, 64);
     if (st != FS_OK) return st;
     fs::Carver ws(workspace);
-    return launch_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
+    return fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
                        ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_, probe, trace);
 }
 
@@ -530,7 +531,7 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
     out.list = ws.take<uint32_t>(n2);
     out.counters = ws.take<int32_t>(64);
     FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));
-    st = launch_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
+    st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
     if (st != FS_OK) return st;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);

@@ -84,8 +84,13 @@ def _match(bank: FrameBank, pa, pb, descriptor: str, threshold, ratio, exact_fp3
     elif descriptor == "binary":
         if bank.desc_bin is None:
             raise ValueError("the frame bank holds no binary descriptors")
+        n_max = int(bank.desc_bin.shape[1])
+        ops = None
+        if api.TENSOR_CORE_MATCHER and n_max <= api.HAMMING_TC_MAX_COLS:
+            # descriptor bits -> +-1 fp16 operand rows of the tensor-core Hamming matcher, once per frame
+            ops = _run(timer, "prepare", lambda: api.hamming_prepare(bank.desc_bin, bank.counts))
         r = _run(timer, "match", lambda: api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True,
-                                                                 ratio=ratio, want_matches1=False))
+                                                                 ratio=ratio, want_matches1=False, operands=ops))
     else:
         raise ValueError("descriptor must be 'float' or 'binary'")
     return r
@@ -268,13 +273,17 @@ def loop_closure_pairs(bank: FrameBank, *, descriptor: str = "binary", min_match
     operands = bank.operands
     if descriptor == "float" and operands is None:
         operands = api.float_prepare(bank.desc_f32, bank.counts)
+    ops_bin = None
+    if descriptor == "binary" and api.TENSOR_CORE_MATCHER and int(bank.desc_bin.shape[1]) <= api.HAMMING_TC_MAX_COLS:
+        ops_bin = api.hamming_prepare(bank.desc_bin, bank.counts)  # once per keyframe, reused by all its pairs
     pp = (camera.cx, camera.cy)
     for o in range(0, lin_all.numel(), chunk):
         lin = lin_all[o:o + chunk]
         a, b = triangular_index(F, lin)
         pa, pb = a.to(torch.int32).to(dev), b.to(torch.int32).to(dev)
         if descriptor == "binary":
-            m = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, want_matches1=False)
+            m = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, want_matches1=False,
+                                        operands=ops_bin)
         else:
             m = api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale, threshold=threshold,
                                       operands=operands)

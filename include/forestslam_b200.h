@@ -83,6 +83,23 @@ int fs_hamming_match(const uint8_t* desc, int n_frames, int n_max, const int32_t
                      int32_t* n_matches,
                      void* workspace, size_t workspace_bytes, fs_stream_t stream);
 
+/* A2 on the tensor cores (guided/all-pairs matching of ORB_SLAM3/src/ORBmatcher.cc:648-762 is the
+ * workload it is for): same reference lines, same outputs bit for bit as fs_hamming_match.  Every descriptor bit
+ * becomes a +-1 fp16 operand, dot = 256 - 2 * hamming is an exact integer in the fp32 tcgen05 accumulator, and the
+ * packed-key row top-3 epilogue of the float matcher orders by (distance, lowest index) like BFMatcher.
+ * fs_hamming_prepare: once per FRAME, desc [n_frames, n_max, 32] u8 -> operands [n_frames, n_max + 1, 512] fp16
+ *   (fs_hamming_operand_bytes); fs_hamming_match_tc: n_max <= 4096 (FS_ERR_UNSUPPORTED above: use fs_hamming_match). */
+size_t fs_hamming_operand_bytes(int n_frames, int n_max);
+int fs_hamming_prepare(const uint8_t* desc, int n_frames, int n_max, const int32_t* counts,
+                       void* operands_fp16, fs_stream_t stream);
+size_t fs_hamming_match_tc_workspace_bytes(int n_pairs, int n_max);
+int fs_hamming_match_tc(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
+                        const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                        int cross_check, float ratio,
+                        int32_t* matches0, int32_t* dist0, int32_t* second0, int32_t* matches1,
+                        int32_t* n_matches,
+                        void* workspace, size_t workspace_bytes, fs_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * A1  float descriptor matching — replaces the tail of SuperGlue.forward that mono_slam.py:100-103 and
  *     stereo_slam.py:210-213, :221-224 consume:

@@ -86,6 +86,39 @@ def test_hamming_batch_ragged(fsb):
         assert np.array_equal(m1[p], inv)
 
 
+@pytest.mark.parametrize("n_max,ratio,cross", [(2000, None, True), (704, 0.8, True), (1111, 0.7, False), (4096, None, True)])
+def test_hamming_tensor_core_equals_popc(fsb, n_max, ratio, cross):
+    """hamming_tc.cu (+-1 fp16 operands on tcgen05, exact integer scores) against hamming.cu (xor + popc): every output
+    array bit for bit, on ragged banks with near-duplicates, exact duplicates (ties) and a bank size that is no
+    multiple of the 128-column tile; one pair is also checked against cv2 itself."""
+    import torch
+    rng = np.random.default_rng(n_max)
+    counts = [n_max, n_max - 37, 1, 0, min(n_max, 655), 2]
+    F = len(counts)
+    bank = np.zeros((F, n_max, 32), np.uint8)
+    for f, c in enumerate(counts):
+        bank[f, :c] = rng.integers(0, 256, (c, 32), dtype=np.uint8)
+    k = min(600, n_max - 37)
+    bank[1, :k] = bank[0, 50:50 + k] ^ np.packbits(rng.random((k, 256)) < 0.06, axis=1)
+    bank[4, :300] = bank[1, :300]                      # exact duplicates of another frame's rows
+    bank[4, 300:330] = bank[4, 0]                      # 31 identical rows inside one frame: index tie-break
+    bank[5, :2] = bank[0, :2]
+    pa = [0, 1, 1, 4, 4, 2, 3, 0, 5, 0, 2]
+    pb = [1, 0, 4, 1, 4, 0, 1, 3, 0, 5, 2]
+    dev_bank = torch.from_numpy(bank).cuda()
+    dev_counts = torch.tensor(counts, dtype=torch.int32).cuda()
+    ref = fsb.hamming_match_batch(dev_bank, dev_counts, pa, pb, cross_check=cross, ratio=ratio, popc=True)
+    ops = fsb.hamming_prepare(dev_bank, dev_counts)
+    got = fsb.hamming_match_batch(None, dev_counts, pa, pb, cross_check=cross, ratio=ratio, operands=ops)
+    for key in ("matches0", "dist0", "second0", "matches1", "n_matches"):
+        assert torch.equal(ref[key], got[key]), key
+    q, t, d = lit.bf_hamming_match(bank[0, :counts[0]], bank[1, :counts[1]])
+    if cross and ratio is None:
+        m0 = got["matches0"][0].cpu().numpy()
+        assert np.array_equal(np.nonzero(m0 >= 0)[0], q) and np.array_equal(m0[q], t)
+        assert np.array_equal(got["dist0"][0].cpu().numpy()[q].astype(np.float32), d)
+
+
 FLOAT_MODES = {"fp32": dict(exact_fp32=True), "split3": dict(split3=True), "top3": dict()}
 
 
