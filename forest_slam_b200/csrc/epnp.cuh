@@ -457,7 +457,7 @@ struct EPnP {
         }
         // MtM = M^T M (mulTransposed order: upper triangle, k ascending, completeSymm); it is symmetric, so the
         // transpose OpenCV hands to JacobiSVD is MtM itself: rows of At end as U^T = `ut`
-        double ut[12 * 12], d[12], vt[12 * 12];
+        double ut[12 * 12], d[12];
         for (int i = 0; i < 12; i++)
             for (int j = i; j < 12; j++) {
                 double s = 0;
@@ -465,7 +465,7 @@ struct EPnP {
                 ut[i * 12 + j] = s;
                 ut[j * 12 + i] = s;
             }
-        jacobi_svd<12, 12, 12>(ut, 12, d, vt);
+        jacobi_svd<12, 12, 12, /*KEEP_V*/ false>(ut, 12, d, nullptr);  // V is not an output of epnp's cvSVD call
         double l_6x10[60], rho[6];
         compute_L_6x10(ut, l_6x10);
         compute_rho(rho);

@@ -45,6 +45,10 @@ __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1,
 
 // ------------------------------------------------------------------------------------------------ engine policy
 struct EPolicy {
+    static constexpr int FIRST_CHUNK = 64;         // speculative iterations per pair in round 0
+    static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
+    static constexpr const char* TUNE_FIRST = "FS_TUNE_E_FIRST_CHUNK";
+    static constexpr const char* TUNE_WARPS = "FS_TUNE_E_SOLVE_WARPS";
     static constexpr int MP = 5;     // model points
     static constexpr int MAXM = 10;  // candidate models per sample
     static constexpr int MD = 9;     // doubles per model
@@ -244,7 +248,7 @@ k_score_essential(const float* __restrict__ mkpts0, const float* __restrict__ mk
 }  // namespace
 
 extern "C" size_t fs_find_essential_workspace_bytes(int n_pairs, int n_max, int max_iters) {
-    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    const rg::Plan pl = rg::make_plan<EPolicy>(n_pairs, max_iters);
     const size_t np = (size_t)(n_pairs > 0 ? n_pairs : 1), nm = (size_t)(n_max > 0 ? n_max : 1);
     return fs::align_up(np * 4 * nm * sizeof(double), 256) + rg::Workspace<EPolicy>::bytes(n_pairs, pl) + 512;
 }
@@ -269,7 +273,7 @@ extern "C" int fs_find_essential_ransac(const float* mkpts0, const float* mkpts1
         fs::set_error("fs_find_essential_ransac: workspace %zu < %zu", workspace_bytes, need);
         return FS_ERR_WORKSPACE;
     }
-    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    const rg::Plan pl = rg::make_plan<EPolicy>(n_pairs, max_iters);
     FS_REQUIRE(pl.pool < (size_t)1 << 30, "n_pairs * max_iters too large");
     fs::Carver cv(workspace);
     double* pts = cv.take<double>((size_t)n_pairs * 4 * n_max);

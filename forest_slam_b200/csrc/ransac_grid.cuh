@@ -26,11 +26,19 @@
 // changes where a pair's slots live, never what they contain.
 #pragma once
 #include "common.cuh"
+#include <stdlib.h>
 #include "cvmath.cuh"
 
 namespace rg {
 
-constexpr int FIRST_CHUNK = 64;   // speculative iterations per pair in round 0
+// Per-policy tuning (Pol::FIRST_CHUNK speculative iterations per pair in round 0, Pol::SOLVE_WARPS_PER_SM solver warps
+// per SM); FS_TUNE_* environment variables override them for measurement runs (read on every call: host side only).
+inline int tune(const char* name, int dflt) {
+    const char* e = getenv(name);
+    if (!e || !*e) return dflt;
+    const int v = atoi(e);
+    return v > 0 ? v : dflt;
+}
 constexpr int SCORE_THREADS = 256;
 constexpr int SOLVE_THREADS = 64;
 constexpr int SELECT_THREADS = 256;
@@ -65,11 +73,17 @@ struct Plan {
     int slots_per_pair;
     int rounds;
     size_t pool;
+    int first_chunk;
+    int solve_warps_per_sm;
 };
 
+template <class Pol>
 inline Plan make_plan(int n_pairs, int max_iters) {
     Plan pl;
     const int mi = max_iters < 1 ? 1 : max_iters;
+    const int FIRST_CHUNK = min(256, max(Pol::SLAB, tune(Pol::TUNE_FIRST, Pol::FIRST_CHUNK) / Pol::SLAB * Pol::SLAB));
+    pl.first_chunk = FIRST_CHUNK;
+    pl.solve_warps_per_sm = tune(Pol::TUNE_WARPS, Pol::SOLVE_WARPS_PER_SM);
     int spp = 256;
     // keep the launch sequence short for very large iteration caps
     while ((mi - FIRST_CHUNK + spp - 1) / spp + 1 > MAX_ROUNDS - 1) spp *= 2;
@@ -118,7 +132,7 @@ struct Workspace {
 template <class Pol>
 __global__ void __launch_bounds__(SELECT_THREADS)
 k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_max, int min_points, int max_iters,
-            double confidence, int pool, Workspace<Pol> ws) {
+            double confidence, int pool, int first_chunk, Workspace<Pol> ws) {
     constexpr int MP = Pol::MP, MAXM = Pol::MAXM, MD = Pol::MD;
     const int lane = threadIdx.x & 31;
     const int p = blockIdx.x * (SELECT_THREADS / 32) + (threadIdx.x >> 5);
@@ -191,7 +205,7 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
         if (allp) {
             chunk = 1;
         } else if (round == 0) {
-            chunk = min(FIRST_CHUNK, nit);
+            chunk = min(first_chunk, nit);
         } else {
             const int prev_active = max(ws.ctl[round - 1].n_active, 1);
             const int share = max((pool / prev_active) & ~(Pol::SLAB - 1), Pol::SLAB);
@@ -330,17 +344,29 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
         const int st_ = fs::ensure_dyn_smem(k_rg_score<Pol>, granted, stage_smem);
         if (st_ != FS_OK) return st_;
     }
+    {
+        // the solvers keep their matrices in local memory (EPnP: 12x12 Jacobi SVD, ~3.8 KB per thread): ask for the
+        // largest L1 the SM can give.  Sticky per device and set during warm-up, never under graph capture.
+        static bool hinted[64];
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+        if (!hinted[dev]) {
+            FS_CUDA(cudaFuncSetAttribute(k_rg_solve<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+            hinted[dev] = true;
+        }
+    }
     const int pool = (int)pl.pool;
     const int sel_grid = (n_pairs + SELECT_THREADS / 32 - 1) / (SELECT_THREADS / 32);
     // solve: one warp per 32 pool slots at most
     int solve_warps = (pool + 31) / 32;
-    solve_warps = min(solve_warps, fs::sm_count() * 4);  // measured: beyond one solver warp per SM sub-partition the
-                                                         // fp64 issue slots are shared and every solve gets slower
+    // E (five-point, fp64-pipe heavy): beyond one solver warp per SM sub-partition the fp64 issue slots are shared and
+    // every solve gets slower; P (EPnP: 12x12 Jacobi SVD in local memory, latency bound at 255 registers) takes two
+    solve_warps = min(solve_warps, fs::sm_count() * pl.solve_warps_per_sm);
     const int solve_grid = (solve_warps + SOLVE_THREADS / 32 - 1) / (SOLVE_THREADS / 32);
     const int score_grid = (pool + Pol::SLAB - 1) / Pol::SLAB;
     for (int r = 0; r <= pl.rounds; r++) {
         k_rg_select<Pol><<<sel_grid, SELECT_THREADS, 0, stream>>>(r, n_pairs, n_corr, n_max, min_points, max_iters,
-                                                                  confidence, pool, ws);
+                                                                  confidence, pool, pl.first_chunk, ws);
         FS_LAUNCH_CHECK("k_rg_select");
         if (r == pl.rounds) break;  // the last select only consumes the last round's counts
         k_rg_solve<Pol><<<solve_grid, SOLVE_THREADS, 0, stream>>>(r, prm, ws);
@@ -349,8 +375,8 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
             k_rg_tail<Pol><<<256, 32, 0, stream>>>(r, prm, ws);
             FS_LAUNCH_CHECK("k_rg_tail");
         }
-        // round 0 uses FIRST_CHUNK slots per pair at most
-        const int sg = (r == 0) ? min(score_grid, (n_pairs * FIRST_CHUNK + Pol::SLAB - 1) / Pol::SLAB) : score_grid;
+        // round 0 uses first_chunk slots per pair at most
+        const int sg = (r == 0) ? min(score_grid, (n_pairs * pl.first_chunk + Pol::SLAB - 1) / Pol::SLAB) : score_grid;
         k_rg_score<Pol><<<sg, SCORE_THREADS, stage_smem, stream>>>(r, prm, ws);
         FS_LAUNCH_CHECK("k_rg_score");
     }

@@ -89,6 +89,10 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
 //            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, warp-reduced count;
 //   finish : mask of the winner (identical arithmetic) + ascending inlier index list.
 struct PPolicy {
+    static constexpr int FIRST_CHUNK = 64;         // speculative iterations per pair in round 0
+    static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
+    static constexpr const char* TUNE_FIRST = "FS_TUNE_P_FIRST_CHUNK";
+    static constexpr const char* TUNE_WARPS = "FS_TUNE_P_SOLVE_WARPS";
     static constexpr int MP = 5;
     static constexpr int MAXM = 1;
     static constexpr int MD = 6;
@@ -486,7 +490,7 @@ extern "C" int fs_score_pnp(const float* points3d, const float* pts2d, const int
 
 
 extern "C" size_t fs_solve_pnp_workspace_bytes(int n_pairs, int, int max_iters) {
-    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    const rg::Plan pl = rg::make_plan<PPolicy>(n_pairs, max_iters);
     return fs::align_up((size_t)(n_pairs > 0 ? n_pairs : 1) * 6 * sizeof(double), 256) +
            rg::Workspace<PPolicy>::bytes(n_pairs, pl) + 512;
 }
@@ -507,7 +511,7 @@ extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, co
         fs::set_error("fs_solve_pnp_ransac: workspace %zu < %zu", workspace_bytes, need);
         return FS_ERR_WORKSPACE;
     }
-    const rg::Plan pl = rg::make_plan(n_pairs, max_iters);
+    const rg::Plan pl = rg::make_plan<PPolicy>(n_pairs, max_iters);
     FS_REQUIRE(pl.pool < (size_t)1 << 30, "n_pairs * max_iters too large");
     fs::Carver cv(workspace);
     double* model = cv.take<double>((size_t)n_pairs * 6);
