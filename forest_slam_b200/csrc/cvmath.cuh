@@ -84,8 +84,17 @@ CVM_HD double hypot_cv(double a, double b) {
 // normalisation), but V itself is neither accumulated nor stored — At and W never depend on it.  EPnP's 12x12
 // decomposition (cvSVD(&MtM, &D, &Ut, 0, ...): V is not an output) uses this: a third less work per rotation and
 // 1152 bytes less local memory per solver thread.
-template <int M, int N, int N1, bool KEEP_V = true>
-CVM_HD void jacobi_svd(double* At, int lda, double* W, double* Vt /* N*N or nullptr */) {
+// PA / PW are pointer-like: double*, or Strided<S> (element i of a thread's matrix at base[i * S]: per-thread matrices
+// interleaved in shared memory, bank-conflict free when S = threads per CTA).
+template <int S>
+struct Strided {
+    double* p;
+    CVM_HD Strided operator+(int o) const { return Strided{p + (size_t)o * S}; }
+    CVM_HD double& operator[](int i) const { return p[(size_t)i * S]; }
+};
+
+template <int M, int N, int N1, bool KEEP_V = true, class PA = double*, class PW = double*>
+CVM_HD void jacobi_svd(PA At, int lda, PW W, double* Vt /* N*N or nullptr */) {
     const bool as_if_v = Vt != nullptr || !KEEP_V;
     const double eps = DBL_EPSILON * 10, minval = DBL_MIN;
     const int max_iter = M > 30 ? M : 30;
@@ -105,8 +114,8 @@ CVM_HD void jacobi_svd(double* At, int lda, double* W, double* Vt /* N*N or null
         bool changed = false;
         for (int i = 0; i < N - 1; i++)
             for (int j = i + 1; j < N; j++) {
-                double* Ai = At + i * lda;
-                double* Aj = At + j * lda;
+                const PA Ai = At + i * lda;
+                const PA Aj = At + j * lda;
                 double a = W[i], p = 0, b = W[j];
                 for (int k = 0; k < M; k++) p += Ai[k] * Aj[k];
                 if (fabs(p) <= eps * sqrt(a * b)) continue;

@@ -226,10 +226,11 @@ struct EPnP {
         }
     }
 
-    CVM_HD void compute_ccs(const double* betas, const double* ut) {
+    // `ut8` = rows 8..11 of U^T (the four right-most singular vectors): the only rows EPnP reads
+    CVM_HD void compute_ccs(const double* betas, const double* ut8) {
         for (int i = 0; i < 4; i++) ccs[i][0] = ccs[i][1] = ccs[i][2] = 0.0f;
         for (int i = 0; i < 4; i++) {
-            const double* v = ut + 12 * (11 - i);
+            const double* v = ut8 + 12 * (3 - i);
             for (int j = 0; j < 4; j++)
                 for (int k = 0; k < 3; k++) ccs[j][k] += betas[i] * v[3 * j + k];
         }
@@ -309,16 +310,16 @@ struct EPnP {
         return sum2 / NP;
     }
 
-    CVM_HD double compute_R_and_t(const double* ut, const double* betas, double R[3][3], double t[3]) {
-        compute_ccs(betas, ut);
+    CVM_HD double compute_R_and_t(const double* ut8, const double* betas, double R[3][3], double t[3]) {
+        compute_ccs(betas, ut8);
         compute_pcs();
         solve_for_sign();
         estimate_R_and_t(R, t);
         return reprojection_error(R, t);
     }
 
-    static CVM_HD void compute_L_6x10(const double* ut, double* l_6x10) {
-        const double* v[4] = {ut + 12 * 11, ut + 12 * 10, ut + 12 * 9, ut + 12 * 8};
+    static CVM_HD void compute_L_6x10(const double* ut8, double* l_6x10) {
+        const double* v[4] = {ut8 + 12 * 3, ut8 + 12 * 2, ut8 + 12 * 1, ut8};
         double dv[4][6][3];
         for (int i = 0; i < 4; i++) {
             int a = 0, b = 1;
@@ -436,8 +437,15 @@ struct EPnP {
         }
     }
 
-    // epnp::compute_pose -> R (row-major 3x3), t
+    // epnp::compute_pose -> R (row-major 3x3), t.  `ut` (144 elements) and `d` (12) are the workspace of the 12x12
+    // decomposition: plain local arrays on the host, per-thread strided shared memory in the RANSAC solver kernel
+    // (local memory there spilled the whole batch's matrices through L1/L2 to DRAM: ransac_pnp.cu).
     CVM_HD void compute_pose(double* R_out, double* t_out) {
+        double ut[12 * 12], d[12];
+        compute_pose_ws<double*, double*>(R_out, t_out, ut, d);
+    }
+    template <class PA, class PW>
+    CVM_HD void compute_pose_ws(double* R_out, double* t_out, PA ut, PW d) {
         choose_control_points();
         compute_barycentric_coordinates();
         double M[2 * NP * 12];
@@ -456,8 +464,7 @@ struct EPnP {
             }
         }
         // MtM = M^T M (mulTransposed order: upper triangle, k ascending, completeSymm); it is symmetric, so the
-        // transpose OpenCV hands to JacobiSVD is MtM itself: rows of At end as U^T = `ut`
-        double ut[12 * 12], d[12];
+        // transpose OpenCV hands to JacobiSVD is MtM itself: rows of At end as U^T
         for (int i = 0; i < 12; i++)
             for (int j = i; j < 12; j++) {
                 double s = 0;
@@ -465,20 +472,23 @@ struct EPnP {
                 ut[i * 12 + j] = s;
                 ut[j * 12 + i] = s;
             }
-        jacobi_svd<12, 12, 12, /*KEEP_V*/ false>(ut, 12, d, nullptr);  // V is not an output of epnp's cvSVD call
+        // V is not an output of epnp's cvSVD call
+        jacobi_svd<12, 12, 12, /*KEEP_V*/ false, PA, PW>(ut, 12, d, nullptr);
+        double ut8[4 * 12];
+        for (int i = 0; i < 48; i++) ut8[i] = ut[96 + i];
         double l_6x10[60], rho[6];
-        compute_L_6x10(ut, l_6x10);
+        compute_L_6x10(ut8, l_6x10);
         compute_rho(rho);
         double Betas[4][4], rep_errors[4], Rs[4][3][3], ts[4][3];
         find_betas_approx_1(l_6x10, rho, Betas[1]);
         gauss_newton(l_6x10, rho, Betas[1]);
-        rep_errors[1] = compute_R_and_t(ut, Betas[1], Rs[1], ts[1]);
+        rep_errors[1] = compute_R_and_t(ut8, Betas[1], Rs[1], ts[1]);
         find_betas_approx_2(l_6x10, rho, Betas[2]);
         gauss_newton(l_6x10, rho, Betas[2]);
-        rep_errors[2] = compute_R_and_t(ut, Betas[2], Rs[2], ts[2]);
+        rep_errors[2] = compute_R_and_t(ut8, Betas[2], Rs[2], ts[2]);
         find_betas_approx_3(l_6x10, rho, Betas[3]);
         gauss_newton(l_6x10, rho, Betas[3]);
-        rep_errors[3] = compute_R_and_t(ut, Betas[3], Rs[3], ts[3]);
+        rep_errors[3] = compute_R_and_t(ut8, Betas[3], Rs[3], ts[3]);
         int N = 1;
         if (rep_errors[2] < rep_errors[1]) N = 2;
         if (rep_errors[3] < rep_errors[N]) N = 3;
@@ -530,6 +540,22 @@ CVM_HD void rodrigues_mat2vec(const double* Rin, double* r) {
 }
 
 // PnPRansacCallback::runKernel for one 5-subset: undistort -> EPnP -> Rodrigues.  model = rvec | tvec.
+// `ut` / `d`: the 144 + 12 element workspace of the 12x12 decomposition (see EPnP::compute_pose_ws)
+template <class PA, class PW>
+CVM_HD void pnp_minimal_epnp5_ws(const CamD& cam, const double (*obj)[3], const float (*img)[2], double* model, PA ut,
+                                 PW d) {
+    float nrm[5][2];
+    for (int i = 0; i < 5; i++) undistort_point_f32(img[i][0], img[i][1], cam, nrm[i][0], nrm[i][1]);
+    EPnP<5> e;
+    e.init(cam, obj, nrm);
+    double R[9], t[3];
+    e.template compute_pose_ws<PA, PW>(R, t, ut, d);
+    rodrigues_mat2vec(R, model);
+    model[3] = t[0];
+    model[4] = t[1];
+    model[5] = t[2];
+}
+
 CVM_HD void pnp_minimal_epnp5(const CamD& cam, const double (*obj)[3], const float (*img)[2], double* model) {
     float nrm[5][2];
     for (int i = 0; i < 5; i++) undistort_point_f32(img[i][0], img[i][1], cam, nrm[i][0], nrm[i][1]);

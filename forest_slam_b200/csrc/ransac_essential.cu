@@ -75,8 +75,9 @@ struct EPolicy {
         cvm::FPSetup fs;
         cvm::DKState dk;
     };
+    static constexpr int SOLVE_SMEM_DOUBLES = 0;  // the five-point solver keeps its state in registers / local memory
     __device__ static int solve(const Params& prm, int p, const int* sub, double* models, int slot, Tail* tail,
-                                int* n_tail) {
+                                int* n_tail, double*) {
         const double* src = prm.pts + (size_t)p * 4 * prm.n_max;
         double q1[5][2], q2[5][2];
 #pragma unroll

@@ -265,10 +265,12 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
 template <class Pol>
 __global__ void __launch_bounds__(SOLVE_THREADS)
 k_rg_solve(int round, typename Pol::Params prm, Workspace<Pol> ws) {
+    extern __shared__ double rg_solve_smem[];  // Pol::SOLVE_SMEM_DOUBLES per thread, interleaved by thread
     const int used = ws.ctl[round].n_used;
     if (used == 0) return;
     const int nwarps = gridDim.x * (SOLVE_THREADS / 32);
     const int w = blockIdx.x * (SOLVE_THREADS / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+#pragma unroll 1  // one copy of the (fully inlined, tens of thousands of instructions) solver: instruction cache
     for (int slot = lane * nwarps + w; slot < used; slot += 32 * nwarps) {
         const int p = ws.slot_pair[slot];
         if (p < 0) continue;
@@ -276,7 +278,7 @@ k_rg_solve(int round, typename Pol::Params prm, Workspace<Pol> ws) {
 #pragma unroll
         for (int i = 0; i < Pol::MP; i++) sub[i] = ws.slot_subset[(size_t)slot * Pol::MP + i];
         const int nm = Pol::solve(prm, p, sub, ws.slot_models + (size_t)slot * Pol::MAXM * Pol::MD, slot, ws.tail,
-                                  &ws.ctl[round].n_tail);
+                                  &ws.ctl[round].n_tail, rg_solve_smem + threadIdx.x);
         if (nm >= 0) ws.slot_nmodels[slot] = nm;  // < 0: deferred to k_rg_tail
     }
 }
@@ -345,15 +347,22 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
         if (st_ != FS_OK) return st_;
     }
     {
-        // the solvers keep their matrices in local memory (EPnP: 12x12 Jacobi SVD, ~3.8 KB per thread): ask for the
-        // largest L1 the SM can give.  Sticky per device and set during warm-up, never under graph capture.
+        // solvers that keep their matrices in local memory ask for the largest L1 the SM can give; a policy with
+        // SOLVE_SMEM_DOUBLES > 0 keeps its hot matrix in shared memory instead (EPnP's 12x12 Jacobi SVD).  Sticky per device and set during warm-up, never under graph capture.
         static bool hinted[64];
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
         if (!hinted[dev]) {
-            FS_CUDA(cudaFuncSetAttribute(k_rg_solve<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+            if (Pol::SOLVE_SMEM_DOUBLES == 0)
+                FS_CUDA(cudaFuncSetAttribute(k_rg_solve<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
             hinted[dev] = true;
         }
+    }
+    const size_t solve_smem = (size_t)Pol::SOLVE_SMEM_DOUBLES * SOLVE_THREADS * sizeof(double);
+    if (solve_smem > 0) {
+        static int granted_solve[64];
+        const int st_ = fs::ensure_dyn_smem(k_rg_solve<Pol>, granted_solve, solve_smem);
+        if (st_ != FS_OK) return st_;
     }
     const int pool = (int)pl.pool;
     const int sel_grid = (n_pairs + SELECT_THREADS / 32 - 1) / (SELECT_THREADS / 32);
@@ -369,7 +378,7 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
                                                                   confidence, pool, pl.first_chunk, ws);
         FS_LAUNCH_CHECK("k_rg_select");
         if (r == pl.rounds) break;  // the last select only consumes the last round's counts
-        k_rg_solve<Pol><<<solve_grid, SOLVE_THREADS, 0, stream>>>(r, prm, ws);
+        k_rg_solve<Pol><<<solve_grid, SOLVE_THREADS, solve_smem, stream>>>(r, prm, ws);
         FS_LAUNCH_CHECK("k_rg_solve");
         if (Pol::HAS_TAIL) {
             k_rg_tail<Pol><<<256, 32, 0, stream>>>(r, prm, ws);

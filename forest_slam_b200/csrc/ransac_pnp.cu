@@ -89,7 +89,7 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
 //            reference's distortion coefficients, float32 reprojection error <= (float)thr^2, warp-reduced count;
 //   finish : mask of the winner (identical arithmetic) + ascending inlier index list.
 struct PPolicy {
-    static constexpr int FIRST_CHUNK = 64;         // speculative iterations per pair in round 0
+    static constexpr int FIRST_CHUNK = 192;        // speculative iterations per pair in round 0 (~390 are typical)
     static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
     static constexpr const char* TUNE_FIRST = "FS_TUNE_P_FIRST_CHUNK";
     static constexpr const char* TUNE_WARPS = "FS_TUNE_P_SOLVE_WARPS";
@@ -114,7 +114,10 @@ struct PPolicy {
         st.carve(smem, prm.n_max);
         st.load(prm.points3d + 3 * (size_t)p * prm.n_max, prm.pts2d + 2 * (size_t)p * prm.n_max, n);
     }
-    __device__ static int solve(const Params& prm, int p, const int* sub, double* model, int, Tail*, int*) {
+    // 12x12 U^T + 12 singular values of EPnP's decomposition, per solver thread, in shared memory (78 KB per CTA of 64)
+    static constexpr int SOLVE_SMEM_DOUBLES = 156;
+    __device__ static int solve(const Params& prm, int p, const int* sub, double* model, int, Tail*, int*,
+                                double* smem) {
         const float* p3 = prm.points3d + 3 * (size_t)p * prm.n_max;
         const float2* p2 = reinterpret_cast<const float2*>(prm.pts2d) + (size_t)p * prm.n_max;
         double obj[5][3];
@@ -130,7 +133,8 @@ struct PPolicy {
             img[i][1] = q.y;
         }
         double m[6];
-        cvm::pnp_minimal_epnp5(prm.cam, obj, img, m);
+        using SP = cvm::Strided<rg::SOLVE_THREADS>;
+        cvm::pnp_minimal_epnp5_ws<SP, SP>(prm.cam, obj, img, m, SP{smem}, SP{smem + 144 * rg::SOLVE_THREADS});
 #pragma unroll
         for (int i = 0; i < 6; i++) model[i] = m[i];
         return 1;
