@@ -149,6 +149,27 @@ def main():
                  "tensor", flop / ms_t / 1e9, pk["tensor_tflops"], "TFLOP/s",
                  "one fp16 tcgen05 pass per direction (2x the algorithmic MMA work, roofline counts 1x); exact integers")
 
+    # ------------------------------------------------------------------ config 5: all-pairs loop-closure matching
+    if on("loopclosure"):
+        from forest_slam_b200 import sequence as seq
+        F, n = 320, 2000  # 51 040 keyframe pairs (the 2000-keyframe job is 1 999 000 pairs of the same shape)
+        desc = torch.randint(0, 256, (F, n, 32), dtype=torch.uint8, generator=g).to(dev)
+        counts = torch.full((F,), n, dtype=torch.int32, device=dev)
+        kp = (torch.rand((F, n, 2), generator=g) * torch.tensor([950.0, 590.0])).to(dev)
+        bank = seq.FrameBank(kpts=kp, counts=counts, desc_bin=desc)
+        npairs = F * (F - 1) // 2
+        for tc in (True, False):
+            fsb.TENSOR_CORE_MATCHER = tc
+            ms = Timer(3)(lambda: seq.loop_closure_pairs(bank, descriptor="binary", min_matches=30))
+            flop = npairs * 2.0 * n * n * 256
+            line("loop_closure_pairs (all-pairs Hamming crossCheck, %s)" % ("tensor cores" if tc else "POPC pipe"),
+                 {"keyframes": F, "kpts": n, "pairs": npairs, "descriptors": "random (no pair passes the 30-match gate)"},
+                 ms, {"flop": flop, "pairs_per_s": npairs / ms * 1e3,
+                      "est_s_for_2000_keyframes_1gpu": 1999000 / (npairs / ms * 1e3)},
+                 "tensor", flop / ms / 1e9, pk["tensor_tflops"], "TFLOP/s",
+                 "whole driver (pair index generation, chunked launches, record assembly), one GPU")
+        fsb.TENSOR_CORE_MATCHER = True
+
     # ------------------------------------------------------------------ A6 back-projection (HBM, 25 B/point)
     if on("backproject"):
         for npts in (1 << 20, 1 << 24):
