@@ -46,7 +46,7 @@ def parse_args():
     ap.add_argument("--exact-fp32", action="store_true", help="CUDA-core fp32 matcher instead of tcgen05")
     ap.add_argument("--split3", action="store_true", help="split-fp16 three-MMA matcher instead of the certified pass")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--lanes", type=int, default=3,
+    ap.add_argument("--lanes", type=int, default=5,
                     help="captured pipelines (own buffers, own stream) the device loop rotates through when --overlap-steps")
     ap.add_argument("--overlap-steps", type=int, default=1,
                     help="1: consecutive steps alternate between two streams (software pipelining across steps)")
