@@ -778,3 +778,32 @@ def Rodrigues(rvec):
     dev = _dev()
     r = _to_cuda(np.asarray(rvec, dtype=np.float64).reshape(1, 3), torch.float64, dev)
     return rodrigues_batch(r)[0].cpu().numpy(), None
+
+
+# ------------------------------------------------------------------------------------------- SURVEY §8(b) names
+# The scope table names the drop-in functions in snake_case; they are the cv2-named wrappers above, argument for argument.
+def bf_match_hamming(d0, d1, *, cross_check: bool = True, ratio: Optional[float] = None):
+    """stereo_slam.py:85, :234 → (queryIdx [K] int32, trainIdx [K] int32, distance [K] float32), ascending queryIdx."""
+    bf = BFMatcher(NORM_HAMMING, crossCheck=cross_check)
+    ms = bf.match(d0, d1) if ratio is None else bf.ratioMatch(d0, d1, ratio)
+    return (np.array([m.queryIdx for m in ms], np.int32), np.array([m.trainIdx for m in ms], np.int32),
+            np.array([m.distance for m in ms], np.float32))
+
+
+def find_essential_mat(p0, p1, *, focal: float, pp, prob: float = 0.999, threshold: float = 1.0,
+                       max_iters: int = 1000):
+    """mono_slam.py:111 → (E, mask)."""
+    return findEssentialMat(p0, p1, focal=focal, pp=pp, method=RANSAC, prob=prob, threshold=threshold,
+                            maxIters=max_iters)
+
+
+def recover_pose(E, p0, p1, *, focal: float, pp, distance_thresh: float = 50.0):
+    """mono_slam.py:112 → (n, R, t, mask)."""
+    return recoverPose(E, p0, p1, focal=focal, pp=pp, distanceThresh=distance_thresh)
+
+
+def solve_pnp_ransac(P3, p2, K, dist, *, reprojection_error: float = 1.0, confidence: float = 0.99,
+                     iterations_count: int = 1000):
+    """stereo_slam.py:294-295 → (ok, rvec, tvec, inliers)."""
+    return solvePnPRansac(P3, p2, K, dist, reprojectionError=reprojection_error, confidence=confidence,
+                          iterationsCount=iterations_count, flags=SOLVEPNP_ITERATIVE)

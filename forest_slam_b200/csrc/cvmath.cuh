@@ -93,7 +93,13 @@ struct Strided {
     CVM_HD double& operator[](int i) const { return p[(size_t)i * S]; }
 };
 
-template <int M, int N, int N1, bool KEEP_V = true, class PA = double*, class PW = double*>
+// WAVEFRONT = true visits the row pairs of a sweep by anti-diagonals d = i + j instead of OpenCV's (i, j) row-major
+// order.  Every row still sees ITS rotations in OpenCV's order ((0,r), (1,r), .., (r-1,r), (r,r+1), .., (r,N-1) have
+// increasing d) and rotations on disjoint row pairs commute exactly, so the result is bit-identical; but the up to N/2
+// pairs of one anti-diagonal are independent, so their dot products (each a serial chain of M dependent additions — the
+// latency that bounds the EPnP solver kernel) run as interleaved chains instead of one after the other.  Kept as a
+// verified option; NOT used by the product path (measured slower, see epnp.cuh).
+template <int M, int N, int N1, bool KEEP_V = true, class PA = double*, class PW = double*, bool WAVEFRONT = false>
 CVM_HD void jacobi_svd(PA At, int lda, PW W, double* Vt /* N*N or nullptr */) {
     const bool as_if_v = Vt != nullptr || !KEEP_V;
     const double eps = DBL_EPSILON * 10, minval = DBL_MIN;
@@ -112,12 +118,40 @@ CVM_HD void jacobi_svd(PA At, int lda, PW W, double* Vt /* N*N or nullptr */) {
     }
     for (int iter = 0; iter < max_iter; iter++) {
         bool changed = false;
-        for (int i = 0; i < N - 1; i++)
-            for (int j = i + 1; j < N; j++) {
+        constexpr int NW = WAVEFRONT ? 2 * N - 3 : N - 1;  // anti-diagonals d = 1 .. 2N-3, or rows i = 0 .. N-2
+        for (int wv = 0; wv < NW; wv++) {
+            constexpr int U = N / 2;  // pairs on one anti-diagonal at most
+            double pw[U];
+            int first, cnt;  // WAVEFRONT: pairs (first + u, d - first - u), u < cnt; else row i = wv, j = i+1 .. N-1
+            if (WAVEFRONT) {
+                const int d = wv + 1;
+                first = d - (N - 1) > 0 ? d - (N - 1) : 0;
+                cnt = (d - 1) / 2 - first + 1;
+#pragma unroll
+                for (int u = 0; u < U; u++) pw[u] = 0;
+                for (int k = 0; k < M; k++) {
+#pragma unroll
+                    for (int u = 0; u < U; u++)
+                        if (u < cnt) pw[u] += (At + (first + u) * lda)[k] * (At + (d - first - u) * lda)[k];
+                }
+            } else {
+                first = wv + 1;
+                cnt = N - 1 - wv;
+            }
+            for (int u = 0; u < cnt; u++) {
+                const int i = WAVEFRONT ? first + u : wv;
+                const int j = WAVEFRONT ? wv + 1 - i : first + u;
                 const PA Ai = At + i * lda;
                 const PA Aj = At + j * lda;
                 double a = W[i], p = 0, b = W[j];
-                for (int k = 0; k < M; k++) p += Ai[k] * Aj[k];
+                if (WAVEFRONT) {
+                    p = 0;
+#pragma unroll
+                    for (int q = 0; q < U; q++)
+                        if (q == u) p = pw[q];  // compile-time indices: pw stays in registers
+                } else {
+                    for (int k = 0; k < M; k++) p += Ai[k] * Aj[k];
+                }
                 if (fabs(p) <= eps * sqrt(a * b)) continue;
                 p *= 2;
                 double beta = a - b, gamma = hypot_cv(p, beta), c, s;
@@ -152,6 +186,7 @@ CVM_HD void jacobi_svd(PA At, int lda, PW W, double* Vt /* N*N or nullptr */) {
                     }
                 }
             }
+        }
         if (!changed) break;
     }
     for (int i = 0; i < N; i++) {

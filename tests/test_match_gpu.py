@@ -119,6 +119,23 @@ def test_hamming_tensor_core_equals_popc(fsb, n_max, ratio, cross):
         assert np.array_equal(got["dist0"][0].cpu().numpy()[q].astype(np.float32), d)
 
 
+def test_hamming_above_4096_uses_popc_and_tc_refuses(fsb):
+    """n_max > 4096 does not fit the 12 column bits of the tensor-core keys: the wrapper takes the POPC kernel (same
+    bits as cv2), the C entry point refuses with FS_ERR_UNSUPPORTED instead of answering wrongly."""
+    import torch
+    d0, d1 = util.binary_descriptors(4200, 300, 21)
+    q, t, d = lit.bf_hamming_match(d0, d1)
+    gq, gt, gd = fsb.bf_match_hamming(d0, d1)
+    assert np.array_equal(q, gq) and np.array_equal(t, gt) and np.array_equal(d, gd)
+    ops = torch.zeros((2, 4225, 512), dtype=torch.float16, device="cuda")
+    with pytest.raises(Exception):
+        fsb.TENSOR_CORE_MATCHER, fsb.HAMMING_TC_MAX_COLS = True, 1 << 20
+        try:
+            fsb.hamming_match_batch(None, torch.tensor([10, 10], dtype=torch.int32).cuda(), [0], [1], operands=ops)
+        finally:
+            fsb.HAMMING_TC_MAX_COLS = 4096
+
+
 FLOAT_MODES = {"fp32": dict(exact_fp32=True), "split3": dict(split3=True), "top3": dict()}
 
 
