@@ -75,6 +75,7 @@ struct EPolicy {
         cvm::FPSetup fs;
         cvm::DKState dk;
     };
+    static constexpr int SOLVE_THREADS = 64;
     static constexpr int SOLVE_SMEM_DOUBLES = 0;  // the five-point solver keeps its state in registers / local memory
     __device__ static int solve(const Params& prm, int p, const int* sub, double* models, int slot, Tail* tail,
                                 int* n_tail, double*) {

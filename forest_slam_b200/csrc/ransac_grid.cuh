@@ -40,7 +40,6 @@ inline int tune(const char* name, int dflt) {
     return v > 0 ? v : dflt;
 }
 constexpr int SCORE_THREADS = 256;
-constexpr int SOLVE_THREADS = 64;
 constexpr int SELECT_THREADS = 256;
 constexpr int MAX_ROUNDS = 40;
 
@@ -263,11 +262,12 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
 
 // ------------------------------------------------------------------------------------------------ solve
 template <class Pol>
-__global__ void __launch_bounds__(SOLVE_THREADS)
+__global__ void __launch_bounds__(Pol::SOLVE_THREADS)
 k_rg_solve(int round, typename Pol::Params prm, Workspace<Pol> ws) {
     extern __shared__ double rg_solve_smem[];  // Pol::SOLVE_SMEM_DOUBLES per thread, interleaved by thread
     const int used = ws.ctl[round].n_used;
     if (used == 0) return;
+    constexpr int SOLVE_THREADS = Pol::SOLVE_THREADS;
     const int nwarps = gridDim.x * (SOLVE_THREADS / 32);
     const int w = blockIdx.x * (SOLVE_THREADS / 32) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
 #pragma unroll 1  // one copy of the (fully inlined, tens of thousands of instructions) solver: instruction cache
@@ -358,6 +358,7 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
             hinted[dev] = true;
         }
     }
+    constexpr int SOLVE_THREADS = Pol::SOLVE_THREADS;
     const size_t solve_smem = (size_t)Pol::SOLVE_SMEM_DOUBLES * SOLVE_THREADS * sizeof(double);
     if (solve_smem > 0) {
         static int granted_solve[64];

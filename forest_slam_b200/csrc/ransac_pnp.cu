@@ -116,6 +116,9 @@ struct PPolicy {
     }
     // 12x12 U^T + 12 singular values of EPnP's decomposition, per solver thread, in shared memory (78 KB per CTA of 64)
     static constexpr int SOLVE_SMEM_DOUBLES = 156;
+    // (measured: CTAs of 32 threads so that five solver warps fit an SM are SLOWER — 33.3k pairs/s at four warps, 31k at
+    // five, against 37k for two CTAs of 64: a fifth warp doubles up on one SM sub-partition and stretches the critical path)
+    static constexpr int SOLVE_THREADS = 64;
     __device__ static int solve(const Params& prm, int p, const int* sub, double* model, int, Tail*, int*,
                                 double* smem) {
         const float* p3 = prm.points3d + 3 * (size_t)p * prm.n_max;
@@ -133,8 +136,8 @@ struct PPolicy {
             img[i][1] = q.y;
         }
         double m[6];
-        using SP = cvm::Strided<rg::SOLVE_THREADS>;
-        cvm::pnp_minimal_epnp5_ws<SP, SP>(prm.cam, obj, img, m, SP{smem}, SP{smem + 144 * rg::SOLVE_THREADS});
+        using SP = cvm::Strided<SOLVE_THREADS>;
+        cvm::pnp_minimal_epnp5_ws<SP, SP>(prm.cam, obj, img, m, SP{smem}, SP{smem + 144 * SOLVE_THREADS});
 #pragma unroll
         for (int i = 0; i < 6; i++) model[i] = m[i];
         return 1;
