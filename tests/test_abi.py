@@ -46,3 +46,18 @@ def test_missing_library_fails_loudly(monkeypatch):
     monkeypatch.setattr(_lib, "LIB_PATH", "/nonexistent/libforestslam_b200.so")
     with pytest.raises(_lib.ForestSlamError):
         _lib.load()
+
+
+def test_survey_8b_names_exist():
+    """the drop-in module exports the named functions with the named keyword arguments."""
+    import inspect
+    from forest_slam_b200 import api
+    want = {"match_mutual_nn": {"threshold", "ratio"}, "bf_match_hamming": {"cross_check", "ratio"},
+            "find_essential_mat": {"focal", "pp", "prob", "threshold", "max_iters"},
+            "recover_pose": {"focal", "pp", "distance_thresh"},
+            "solve_pnp_ransac": {"reprojection_error", "confidence", "iterations_count"},
+            "backproject_stereo": {"baseline", "zmin", "zmax"}}
+    for name, kws in want.items():
+        fn = getattr(api, name)
+        assert callable(fn), name
+        assert kws <= set(inspect.signature(fn).parameters), (name, kws - set(inspect.signature(fn).parameters))
