@@ -313,3 +313,23 @@ def test_loop_closure_all_pairs(fsb):
         else:
             assert ni == -1
     assert n_verified >= 6 and n_exact >= n_verified - 1
+
+
+def test_survey_8b_names(fsb):
+    """The snake_case drop-in names of SURVEY §8(b) give the same results as the reference's literal cv2 calls."""
+    p0, p1, _, _, _ = util.two_view(1200, 7002, outliers=0.1)
+    E_cv, mask_cv = lit.find_essential(p0, p1)
+    E, mask = fsb.find_essential_mat(p0, p1, focal=util.FOCAL, pp=util.PP)
+    assert np.array_equal(mask, mask_cv) and np.abs(E - E_cv).max() < 1e-6
+    ng_cv, R_cv, t_cv, pm_cv = lit.recover_pose(E_cv, p0, p1)
+    ng, R, t, pm = fsb.recover_pose(E, p0, p1, focal=util.FOCAL, pp=util.PP)
+    assert ng == ng_cv and np.array_equal(pm, pm_cv) and lit.angle_error_mat(R, R_cv) < ROT_TOL
+    P3, p2, _, _ = util.pnp_scene(300, 8001, outliers=0.1)
+    ok_cv, rvec_cv, tvec_cv, inl_cv = lit.solve_pnp_ransac(P3, p2)
+    ok, rvec, tvec, inl = fsb.solve_pnp_ransac(P3, p2, lit.K0, lit.DIST_L)
+    assert ok == ok_cv and np.array_equal(inl, inl_cv)
+    assert lit.angle_error_mat(fsb.Rodrigues(rvec)[0], fsb.Rodrigues(rvec_cv)[0]) < ROT_TOL
+    d0, d1 = util.binary_descriptors(2048, 1777, 2)
+    q, t_, d = lit.bf_hamming_match(d0, d1)
+    gq, gt, gd = fsb.bf_match_hamming(d0, d1)
+    assert np.array_equal(q, gq) and np.array_equal(t_, gt) and np.array_equal(d, gd)
