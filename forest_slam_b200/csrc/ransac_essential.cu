@@ -45,7 +45,7 @@ __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1,
 
 // ------------------------------------------------------------------------------------------------ engine policy
 struct EPolicy {
-    static constexpr int FIRST_CHUNK = 64;         // speculative iterations per pair in round 0
+    static constexpr int FIRST_CHUNK = 48;         // speculative iterations per pair in round 0 (~30 are typical; profiles/r01zv)
     static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
     static constexpr const char* TUNE_FIRST = "FS_TUNE_E_FIRST_CHUNK";
     static constexpr const char* TUNE_WARPS = "FS_TUNE_E_SOLVE_WARPS";
