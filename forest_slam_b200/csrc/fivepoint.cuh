@@ -1,5 +1,6 @@
 // fivepoint.cuh — Nister's five-point essential-matrix solver, as OpenCV's EMEstimatorCallback::runKernel
-// (calib3d/five-point.cpp) executes it; one thread per 5-subset.  Replaces the minimal solver inside
+// (calib3d/five-point.cpp, OpenCV, Apache-2.0 licence) executes it; one thread per 5-subset.  A restatement of that
+// routine's arithmetic (not of any file under /root/reference).  Replaces the minimal solver inside
 //   cv2.findEssentialMat(..., method=cv2.RANSAC)          ros_ws/src/mono_slam.py:111
 //
 // Stage-by-stage fidelity (pinned by oracle/opencv_replay.py against cv2 4.13):
@@ -7,9 +8,11 @@
 //   2. null space = rows 5..8 of Vt of SVD::compute(Q, FULL_UV): OpenCV's Jacobi SVD completes the basis
 //      with fixed pseudo-random sign vectors, so the basis (hence the hidden variable z and the order in
 //      which Durand-Kerner returns the roots) is a deterministic function of the row space of Q;
-//   3. 10 cubic constraints (det E = 0, 2 E E^T E - tr(E E^T) E = 0) in Nister's monomial order, reduced by
-//      Gauss-Jordan with partial pivoting (OpenCV: A[:, :10].inv() * A[:, 10:]);
-//   4. det of the 3x3 polynomial matrix B(z) -> degree-10 polynomial;
+//   3. 10 cubic constraints (det E = 0, 2 E E^T E - tr(E E^T) E = 0): OpenCV's getCoeffMat is GENERATED straight-line
+//      code; its term and factor order is read out of the cv2 4.13.0 binary with an instruction trace
+//      (oracle/cvtrace/) and kept as a table (fivepoint_cv_tables.inc), so every A[k] is bit-identical to cv2's;
+//      reduced by cv::solve(LU) (what MatExpr turns A[:, :10].inv() * A[:, 10:] into);
+//   4. det of the 3x3 polynomial matrix B(z) -> degree-10 polynomial, same table treatment;
 //   5. cv::solvePoly's Durand-Kerner (Gauss-Seidel order, start (1+i)^k).  OpenCV always runs 300 sweeps;
 //      the iterates reach their rounding-noise floor after ~20 and then only jitter in the last bits, so the
 //      sweep loop stops once the largest update stalls (see dk_solve);
@@ -284,12 +287,24 @@ __device__ inline void dk_advance_warp(const double* coeffs, DKState& st, int un
 }
 #endif
 
-// polynomial helpers, coefficient k multiplies z^k
-template <int NA, int NB>
-CVM_HD void pmul_acc(const double* a, const double* b, double* out, double sign) {
-    for (int i = 0; i < NA; i++)
-        for (int j = 0; j < NB; j++) out[i + j] += sign * (a[i] * b[j]);
-}
+// Term tables of OpenCV's two GENERATED straight-line blocks (getCoeffMat, det B(z)): one copy for the host build of
+// this header (tests/host_harness) and one in constant memory for the kernels (every thread of a warp walks the table
+// in lock-step, so the reads are broadcasts).
+#define FS_TABLE_END };
+#define FS_TABLE_BEGIN(T, name, n) static const T name##_h[n] = {
+#include "fivepoint_cv_tables.inc"
+#undef FS_TABLE_BEGIN
+#ifdef __CUDACC__
+#define FS_TABLE_BEGIN(T, name, n) static __constant__ T name##_d[n] = {
+#include "fivepoint_cv_tables.inc"
+#undef FS_TABLE_BEGIN
+#endif
+#undef FS_TABLE_END
+#ifdef __CUDA_ARCH__
+#define FP_TAB(name) name##_d
+#else
+#define FP_TAB(name) name##_h
+#endif
 
 // What the stages after the polynomial need from the stages before it.
 struct FPSetup {
@@ -298,8 +313,24 @@ struct FPSetup {
     double coeffs[11]; // det B(z), coefficient k multiplies z^k
 };
 
+// One output of a term table: fold(+/-) of left-associated products, in the order the cv2 binary evaluates them.
+// NF = factors per term slot (4 for getCoeffMat, 3 for det B(z)); 255 = factor absent; bit 7 of f0 = subtract.
+template <int NF>
+CVM_HD double fp_eval_terms(const unsigned char* t, int n_terms, const double* L) {
+    double acc = 0;
+    for (int i = 0; i < n_terms; i++, t += NF) {
+        const int f0 = t[0];
+        double p = L[f0 & 127] * L[t[1]];
+        if (t[2] != 255) p = p * L[t[2]];
+        if (NF == 4 && t[NF - 1] != 255) p = p * L[t[NF - 1]];
+        if (i == 0) acc = (f0 & 128) ? -p : p;
+        else acc = (f0 & 128) ? acc - p : acc + p;
+    }
+    return acc;
+}
+
 // stages 1-4: q1, q2 = 5 normalised correspondences (x, y).  Returns false when the constraint matrix is singular
-// (OpenCV's inv() returns zeros -> no usable model).
+// (cv::solve returns false and zero-fills -> no usable model).
 CVM_HD bool five_point_setup(const double (*q1)[2], const double (*q2)[2], FPSetup& fs) {
     FP_TICK(0);
     // 1-2. Q and its completed right singular basis
@@ -316,127 +347,77 @@ CVM_HD bool five_point_setup(const double (*q1)[2], const double (*q2)[2], FPSet
     for (int k = 0; k < 36; k++) fs.EE[k] = EE[k];
     FP_TICK(1);
 
-    // 3. constraints.  Lq[s][m]: quadratic form of (E E^T - 1/2 tr(E E^T) I), symmetric index s of (i, k)
+    // 3. getCoeffMat: the 10 cubic constraints (det E = 0, 2 E E^T E - tr(E E^T) E = 0) expanded over
+    //    e[], e[]^2, e[]^3 exactly as OpenCV's generated code sums them
     double A[10][20];
-    for (int r = 0; r < 10; r++)
-        for (int c = 0; c < 20; c++) A[r][c] = 0;
     {
-        double Lq[6][10];
-        const int si[6] = {0, 0, 0, 1, 1, 2}, sk[6] = {0, 1, 2, 1, 2, 2};
-        for (int s = 0; s < 6; s++) {
-            for (int m = 0; m < 10; m++) Lq[s][m] = 0;
-            for (int l = 0; l < 3; l++)
-                for (int a = 0; a < 4; a++)
-                    for (int b = 0; b < 4; b++)
-                        Lq[s][t2(a, b)] += EE[a * 9 + 3 * si[s] + l] * EE[b * 9 + 3 * sk[s] + l];
+        double L[108 + 4];
+        for (int k = 0; k < 36; k++) {
+            const double e = EE[k], e2 = e * e;
+            L[k] = e;
+            L[36 + k] = e2;
+            L[72 + k] = e2 * e;
         }
-        for (int m = 0; m < 10; m++) {
-            const double tr = 0.5 * (Lq[0][m] + Lq[3][m] + Lq[5][m]);
-            Lq[0][m] -= tr;
-            Lq[3][m] -= tr;
-            Lq[5][m] -= tr;
-        }
-        const int sym[3][3] = {{0, 1, 2}, {1, 3, 4}, {2, 4, 5}};
-        for (int i = 0; i < 3; i++)
-            for (int j = 0; j < 3; j++) {
-                double* row = A[3 * i + j];
-                for (int k = 0; k < 3; k++) {
-                    const double* L = Lq[sym[i][k]];
-                    for (int m = 0; m < 10; m++)
-                        for (int c = 0; c < 4; c++) row[t3(m, c)] += L[m] * EE[c * 9 + 3 * k + j];
-                }
+        for (int k = 0; k < 4; k++) L[108 + k] = FP_TAB(FP_COEF_CONST)[k];
+        // getCoeffMat ends by permuting its columns (left block of the system = computed columns
+        // 6 8 18 15 12 5 14 7 4 11, right block = 19 13 1 16 17 3 10 9 2 0)
+        for (int r = 0; r < 10; r++)
+            for (int c = 0; c < 20; c++) {
+                const int k = 20 * r + FP_TAB(FP_COEF_PERM)[c];
+                const int s = FP_TAB(FP_COEF_START)[k], e = FP_TAB(FP_COEF_START)[k + 1];
+                A[r][c] = fp_eval_terms<4>(FP_TAB(FP_COEF_TERMS) + 4 * s, e - s, L);
             }
-        // det(E) = E[0,:] . (E[1,:] x E[2,:])
-        double cr[3][10];
-        for (int d = 0; d < 3; d++) {
-            for (int m = 0; m < 10; m++) cr[d][m] = 0;
-            const int u = (d + 1) % 3, v = (d + 2) % 3;
-            for (int a = 0; a < 4; a++)
-                for (int b = 0; b < 4; b++)
-                    cr[d][t2(a, b)] += EE[a * 9 + 3 + u] * EE[b * 9 + 6 + v] - EE[a * 9 + 3 + v] * EE[b * 9 + 6 + u];
-        }
-        for (int d = 0; d < 3; d++)
-            for (int m = 0; m < 10; m++)
-                for (int c = 0; c < 4; c++) A[9][t3(m, c)] += cr[d][m] * EE[c * 9 + d];
     }
 
     FP_TICK(2);
-    // Gauss-Jordan with partial pivoting on [A(:, 0:10) | A(:, 10:20)].  Fully unrolled: the only dynamic index is the
-    // pivot row; the row operations of one elimination step are independent of each other and pipeline freely.
-#pragma unroll
-    for (int c = 0; c < 10; c++) {
-        int piv = c;
-        double best = fabs(A[c][c]);
-#pragma unroll
-        for (int r = c + 1; r < 10; r++) {
-            const double v = fabs(A[r][c]);
-            if (v > best) {
-                best = v;
-                piv = r;
+    // A[:, :10].inv() * A[:, 10:] is folded by cv::MatExpr into cv::solve(A[:, :10], A[:, 10:], DECOMP_LU) =
+    // hal::LU64f: elimination with partial pivoting applied to the right-hand side, then back-substitution.
+    // Left block: A[r][0..9]; right block (the result): A[r][10..19].
+    for (int i = 0; i < 10; i++) {
+        int k = i;
+        for (int j = i + 1; j < 10; j++)
+            if (fabs(A[j][i]) > fabs(A[k][i])) k = j;
+        if (fabs(A[k][i]) < DBL_EPSILON * 100) return false;
+        if (k != i) {
+            for (int j = i; j < 20; j++) {
+                const double t = A[i][j];
+                A[i][j] = A[k][j];
+                A[k][j] = t;
             }
         }
-        if (best < DBL_MIN) return false;  // singular: OpenCV's inv() returns zeros -> no usable model
-        double prow[20];
-#pragma unroll
-        for (int k = c; k < 20; k++) prow[k] = A[piv][k];
-        if (piv != c) {
-#pragma unroll
-            for (int k = c; k < 20; k++) A[piv][k] = A[c][k];
-        }
-        const double inv = 1. / prow[c];
-#pragma unroll
-        for (int k = c; k < 20; k++) {
-            prow[k] *= inv;
-            A[c][k] = prow[k];
-        }
-#pragma unroll
-        for (int r = 0; r < 10; r++) {
-            if (r == c) continue;
-            const double f = A[r][c];
-            if (f != 0) {
-#pragma unroll
-                for (int k = c; k < 20; k++) A[r][k] -= f * prow[k];
-            }
+        const double d = -1 / A[i][i];
+        for (int j = i + 1; j < 10; j++) {
+            const double alpha = A[j][i] * d;
+            for (int c = i + 1; c < 10; c++) A[j][c] += alpha * A[i][c];
+            for (int c = 10; c < 20; c++) A[j][c] += alpha * A[i][c];
         }
     }
+    for (int i = 9; i >= 0; i--)
+        for (int j = 10; j < 20; j++) {
+            double s = A[i][j];
+            for (int k = i + 1; k < 10; k++) s -= A[i][k] * A[k][j];
+            A[i][j] = s / A[i][i];
+        }
 
     FP_TICK(3);
-    // 4. B(z): rows (4,5), (6,7), (8,9) -> [cubic | cubic | quartic], highest power first (OpenCV layout b[13])
+    // 4. B(z): rows (4,5), (6,7), (8,9) -> [cubic | cubic | quartic], highest power first (OpenCV layout b[13]);
+    //    row1 - row2 with the structural zeros of OpenCV's shifted rows (0 - x = -x and x - 0 = x exactly)
     double (*B)[13] = fs.B;
     for (int i = 0; i < 3; i++) {
         const double* r1 = &A[4 + 2 * i][10];
         const double* r2 = &A[5 + 2 * i][10];
         double* b = B[i];
-        b[0] = -r2[0];        b[1] = r1[0] - r2[1]; b[2] = r1[1] - r2[2]; b[3] = r1[2];
-        b[4] = -r2[3];        b[5] = r1[3] - r2[4]; b[6] = r1[4] - r2[5]; b[7] = r1[5];
-        b[8] = -r2[6];        b[9] = r1[6] - r2[7]; b[10] = r1[7] - r2[8]; b[11] = r1[8] - r2[9]; b[12] = r1[9];
+        b[0] = 0.0 - r2[0];   b[1] = r1[0] - r2[1]; b[2] = r1[1] - r2[2]; b[3] = r1[2];
+        b[4] = 0.0 - r2[3];   b[5] = r1[3] - r2[4]; b[6] = r1[4] - r2[5]; b[7] = r1[5];
+        b[8] = 0.0 - r2[6];   b[9] = r1[6] - r2[7]; b[10] = r1[7] - r2[8]; b[11] = r1[8] - r2[9]; b[12] = r1[9];
     }
-    double* coeffs = fs.coeffs;
+    // det B(z): c[0..10], each a sum of signed triple products of b[] in OpenCV's order
     {
-        // ascending-power copies of the blocks
-        double P[3][3][5];
-        for (int i = 0; i < 3; i++) {
-            for (int k = 0; k < 4; k++) {
-                P[i][0][k] = B[i][3 - k];
-                P[i][1][k] = B[i][7 - k];
-            }
-            P[i][0][4] = P[i][1][4] = 0;
-            for (int k = 0; k < 5; k++) P[i][2][k] = B[i][12 - k];
+        const double* bf = &B[0][0];
+        for (int k = 0; k < 11; k++) {
+            const int s = FP_TAB(FP_POLY_START)[k], e = FP_TAB(FP_POLY_START)[k + 1];
+            fs.coeffs[k] = fp_eval_terms<3>(FP_TAB(FP_POLY_TERMS) + 3 * s, e - s, bf);
         }
-        for (int k = 0; k < 11; k++) coeffs[k] = 0;
-        // det = sum_j B0j * cofactor_j ; minors of rows 1,2
-        double m0[8], m1[8], m2[7];
-        for (int k = 0; k < 8; k++) m0[k] = m1[k] = 0;
-        for (int k = 0; k < 7; k++) m2[k] = 0;
-        pmul_acc<4, 5>(P[1][1], P[2][2], m0, 1.);   // B11*B22
-        pmul_acc<5, 4>(P[1][2], P[2][1], m0, -1.);  // - B12*B21
-        pmul_acc<4, 5>(P[1][0], P[2][2], m1, 1.);   // B10*B22
-        pmul_acc<5, 4>(P[1][2], P[2][0], m1, -1.);  // - B12*B20
-        pmul_acc<4, 4>(P[1][0], P[2][1], m2, 1.);   // B10*B21
-        pmul_acc<4, 4>(P[1][1], P[2][0], m2, -1.);  // - B11*B20
-        pmul_acc<4, 8>(P[0][0], m0, coeffs, 1.);
-        pmul_acc<4, 8>(P[0][1], m1, coeffs, -1.);
-        pmul_acc<5, 7>(P[0][2], m2, coeffs, 1.);
     }
     FP_TICK(4);
     return true;
@@ -462,14 +443,20 @@ CVM_HD int five_point_models(const FPSetup& fs, const Cplx* roots, int n, double
         const double* xy1 = vt + 6;
         if (fabs(xy1[2]) < 1e-10) continue;
         const double x = xy1[0] / xy1[2], y = xy1[1] / xy1[2];
+        // Evec = EE.col(0)*x + EE.col(1)*y + EE.col(2)*z + EE.col(3); Evec /= norm(Evec), as the cv2 binary runs it on
+        // an FMA-capable x86 host: addWeighted = fma(a, alpha, b*beta) + 0, scaleAdd = fma(c, z, .), add; norm =
+        // sequential sum of squares with the 9th element folded by fma (tail of the 4-wide loop); scale by 1/norm.
         double* e = models + 9 * count;
-        double nrm = 0;
+        double acc = 0;
         for (int k = 0; k < 9; k++) {
-            e[k] = EE[k] * x + EE[9 + k] * y + EE[18 + k] * z1 + EE[27 + k];
-            nrm += e[k] * e[k];
+            double v = fma(EE[k], x, EE[9 + k] * y) + 0.0;
+            v = fma(EE[18 + k], z1, v);
+            v = v + EE[27 + k];
+            e[k] = v;
+            acc = k < 8 ? acc + v * v : fma(v, v, acc);
         }
-        nrm = sqrt(nrm);
-        for (int k = 0; k < 9; k++) e[k] /= nrm;
+        const double inv = 1.0 / sqrt(acc);
+        for (int k = 0; k < 9; k++) e[k] = e[k] * inv;
         count++;
     }
     FP_TICK(6);

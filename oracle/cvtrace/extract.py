@@ -7,6 +7,8 @@ import pickle
 
 A_LOOP = 0x15b8c80      # ep2/ep3 loop head of getCoeffMat (cv2 4.13.0.92 manylinux x86_64 wheel)
 A_BODY = 0x15b8ca6      # first instruction after the loop
+A_PERM = 0x15de542      # getCoeffMat's closing column permutation (table of 20 ints in .rodata, copied to the stack)
+A_PERM_TABLE = 0x3a5dd10
 P_BODY = 0x15e8acf      # first instruction of the c[] block
 POLY_CALL = 0x6fa8c0    # cv::solvePoly
 
@@ -28,7 +30,11 @@ def main(tr):
     g = S.T["gpr"][kA]
     eb, ab = int(g[GIDX["rax"]]), int(g[GIDX["rdx"]])
     C = Canon(S, eb, 36)
-    outs = {(a - ab) // 8: nd for (k, a, nd) in S.store_log if ab <= a < ab + 1600}
+    kPerm = first(va, A_PERM)
+    outs = {(a - ab) // 8: nd for (k, a, nd) in S.store_log if ab <= a < ab + 1600 and k < kPerm}
+    perm = list(struct.unpack_from("<20i", S.so, A_PERM_TABLE))
+    assert sorted(perm) == list(range(20))
+    print("column permutation (dest column j <- computed column perm[j]):", perm)
     ev = np.zeros(36)
     for n in S.nodes:
         if n[0] == "in" and n[1] is not None and eb <= n[1] < eb + 288 and n[3] != -1:
@@ -88,7 +94,7 @@ def main(tr):
         ok = C3.evaluate(t, bv) == u2f(S3.nodes[cand[cb + 8 * k][1]][3])
         print("c", k, len(t), ok)
         poly[k] = t
-    pickle.dump({"coef": coef, "poly": poly, "e": ev, "b": bv,
+    pickle.dump({"coef": coef, "poly": poly, "perm": perm, "e": ev, "b": bv,
                  "A": [u2f(S.nodes[outs[k]][3]) for k in range(200)],
                  "c": [u2f(S3.nodes[cand[cb + 8 * k][1]][3]) for k in range(11)]}, open(tr + ".tables.pkl", "wb"))
 

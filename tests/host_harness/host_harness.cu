@@ -12,6 +12,16 @@ int hh_five_point(const double* q1, const double* q2, double* models) {
     return cvm::five_point((const double(*)[2])q1, (const double(*)[2])q2, models);
 }
 
+// stages 1-4 alone: null-space basis EE[36], B(z) [39], polynomial c[11] (pinned against the traced cv2 values)
+int hh_five_point_setup(const double* q1, const double* q2, double* EE, double* B, double* c) {
+    cvm::FPSetup fs;
+    const bool ok = cvm::five_point_setup((const double(*)[2])q1, (const double(*)[2])q2, fs);
+    for (int k = 0; k < 36; k++) EE[k] = fs.EE[k];
+    for (int k = 0; k < 39; k++) B[k] = (&fs.B[0][0])[k];
+    for (int k = 0; k < 11; k++) c[k] = fs.coeffs[k];
+    return ok ? 1 : 0;
+}
+
 void hh_ransac_subsets(int count, int n_iters, int* out) {
     cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
     for (int it = 0; it < n_iters; it++) {
