@@ -22,6 +22,58 @@ int hh_five_point_setup(const double* q1, const double* q2, double* EE, double* 
     return ok ? 1 : 0;
 }
 
+// cv::solvePoly restatement alone: roots (re, im) in slot order; max_iters = 300 reproduces OpenCV's fixed sweep count
+int hh_solve_poly(const double* coeffs, double* roots, int max_iters, int early_stop) {
+    cvm::Cplx r[10];
+    int n;
+    if (early_stop) n = cvm::dk_solve(coeffs, r, max_iters);
+    else {
+        cvm::DKState st;
+        cvm::dk_init(coeffs, st);
+        // plain 300 sweeps: advance one sweep at a time and ignore the stop rule
+        for (int it = 1; it <= max_iters; it++) {
+            st.stalled = 0; st.floor_md = DBL_MAX;
+            cvm::dk_advance(coeffs, st, it);
+        }
+        n = cvm::dk_finish(st, r);
+    }
+    for (int i = 0; i < n; i++) { roots[2 * i] = r[i].re; roots[2 * i + 1] = r[i].im; }
+    return n;
+}
+
+// exact-cycle statistics of the Durand-Kerner iteration: first sweep t at which the full state equals the state
+// p sweeps earlier (p <= 16); returns t (or -1), *period = p
+int hh_dk_cycle(const double* coeffs, int* period) {
+    cvm::DKState st;
+    cvm::dk_init(coeffs, st);
+    cvm::Cplx hist[17][10];
+    for (int it = 1; it <= 300; it++) {
+        st.stalled = 0; st.floor_md = DBL_MAX;
+        cvm::dk_advance(coeffs, st, it);
+        for (int i = 0; i < 10; i++) hist[it % 17][i] = st.r[i];
+        for (int p = 1; p <= 16 && p < it; p++) {
+            bool same = true;
+            for (int i = 0; i < st.n; i++)
+                same &= hist[(it - p) % 17][i].re == st.r[i].re && hist[(it - p) % 17][i].im == st.r[i].im;
+            if (same) { *period = p; return it; }
+        }
+    }
+    *period = 0;
+    return -1;
+}
+
+// every sweep's state: states[(it-1)*20 + 2*i + {0,1}], it = 1..300; returns the degree solved
+int hh_dk_states(const double* coeffs, double* states) {
+    cvm::DKState st;
+    cvm::dk_init(coeffs, st);
+    for (int it = 1; it <= 300; it++) {
+        st.stalled = 0; st.floor_md = DBL_MAX;
+        cvm::dk_advance(coeffs, st, it);
+        for (int i = 0; i < 10; i++) { states[(it - 1) * 20 + 2 * i] = st.r[i].re; states[(it - 1) * 20 + 2 * i + 1] = st.r[i].im; }
+    }
+    return st.n;
+}
+
 void hh_ransac_subsets(int count, int n_iters, int* out) {
     cvm::RNG rng(0xFFFFFFFFFFFFFFFFull);
     for (int it = 0; it < n_iters; it++) {
