@@ -20,19 +20,6 @@
 
 namespace cvm {
 
-// quadratic monomial index of (a, b) and cubic monomial index of (quad m, c); variables 0=x 1=y 2=z 3=1.
-// Cubic order = the column order of OpenCV's constraint matrix:
-// x3 y3 x2y xy2 x2z x2 y2z y2 xyz xy | xz2 xz x yz2 yz y z3 z2 z 1
-CVM_HD int t2(int a, int b) {
-    constexpr int T[4][4] = {{0, 1, 2, 3}, {1, 4, 5, 6}, {2, 5, 7, 8}, {3, 6, 8, 9}};
-    return T[a][b];
-}
-CVM_HD int t3(int m, int c) {
-    constexpr int T[10][4] = {{0, 2, 4, 5},    {2, 3, 8, 9},     {4, 8, 10, 11},   {5, 9, 11, 12},  {3, 1, 6, 7},
-                              {8, 6, 13, 14},  {9, 7, 14, 15},   {10, 13, 16, 17}, {11, 14, 17, 18}, {12, 15, 18, 19}};
-    return T[m][c];
-}
-
 struct Cplx {
     double re, im;
 };
@@ -65,8 +52,7 @@ CVM_HD bool cplx_is_zero(Cplx d) {
 #endif
 }
 
-// Durand-Kerner state of one polynomial: roots + the stop-rule bookkeeping, so that a run can be suspended after a
-// sweep budget and resumed elsewhere (ransac_essential.cu hands the rare slow cases to a warp-cooperative tail).
+// Durand-Kerner state of one polynomial (a run can be advanced in pieces: tests/host_harness steps it sweep by sweep).
 struct DKState {
     Cplx r[10];
     double floor_md;
@@ -208,80 +194,6 @@ CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
     dk_advance(coeffs, st, max_iters);
     return dk_finish(st, roots);
 }
-
-#ifdef __CUDACC__
-// Warp-cooperative continuation of a suspended run: lane i owns root i.  The arithmetic of every root update is the
-// scalar loop's, operation for operation (numerator Horner chain, denominator factors in slot order with the roots
-// already updated in this sweep, complex division), so a run finished here ends in exactly the state the scalar loop
-// would have reached; what changes is the critical path of a sweep: the N numerators and all "already updated"
-// denominator factors are evaluated side by side, leaving sum_i (N - i) dependent complex products per sweep instead
-// of ~2 N^2 issued from one thread.  All 32 lanes must call.
-__device__ inline void dk_advance_warp(const double* coeffs, DKState& st, int until_iter) {
-    const int lane = threadIdx.x & 31;
-    const int N = st.n;
-    const unsigned full = 0xffffffffu;
-    Cplx r = st.r[lane < 10 ? lane : 0];
-    double floor_md = st.floor_md;
-    int stalled = st.stalled, iter = st.iter;
-    bool done = false;
-    for (; iter < until_iter && !done; iter++) {
-        Cplx num = {coeffs[N], 0};
-        for (int j = 0; j < N; j++) {
-            num = cmul(num, r);
-            num.re += coeffs[N - j - 1];
-        }
-        const Cplx p = r;
-        Cplx ro[10];  // every slot's pre-sweep value
-#pragma unroll
-        for (int j = 0; j < 10; j++) {
-            ro[j].re = __shfl_sync(full, r.re, j);
-            ro[j].im = __shfl_sync(full, r.im, j);
-        }
-        Cplx denom = {coeffs[N], 0};  // factors of slots already updated in this sweep, absorbed as they appear
-        double mag2 = 0;
-        // Always 10 steps and no shuffle under a branch (a shuffle the compiler cannot prove convergent costs a
-        // warp-sync sequence): slots >= N only produce values nobody reads.
-#pragma unroll
-        for (int i = 0; i < 10; i++) {
-            // slot i: remaining factors (slots j > i, still at their pre-sweep values), then the update
-            Cplx dch = denom;
-#pragma unroll
-            for (int j = i + 1; j < 10; j++) {
-                const Cplx d = {p.re - ro[j].re, p.im - ro[j].im};
-                const Cplx nd = cmul(dch, d);
-                const bool nz = (d.re != 0 || d.im != 0) && j < N;
-                dch.re = nz ? nd.re : dch.re;
-                dch.im = nz ? nd.im : dch.im;
-            }
-            const Cplx q = cdiv(num, dch);
-            const Cplx nr = {p.re - q.re, p.im - q.im};
-            const double bre = __shfl_sync(full, nr.re, i), bim = __shfl_sync(full, nr.im, i);
-            const Cplx d = {p.re - bre, p.im - bim};
-            const Cplx nd = cmul(denom, d);
-            const bool absorb = lane > i && (d.re != 0 || d.im != 0);
-            denom.re = absorb ? nd.re : denom.re;
-            denom.im = absorb ? nd.im : denom.im;
-            const bool mine = lane == i;
-            r.re = mine ? nr.re : r.re;
-            r.im = mine ? nr.im : r.im;
-            mag2 = mine ? q.re * q.re + q.im * q.im : mag2;
-        }
-        double max_diff = lane < N ? sqrt(mag2) : 0.0;
-#pragma unroll
-        for (int o = 16; o >= 1; o >>= 1) max_diff = fmax(max_diff, __shfl_xor_sync(full, max_diff, o));
-        done = __any_sync(full, dk_stop_rule(max_diff, iter, floor_md, stalled));  // (uniform; the vote tells the compiler)
-    }
-#pragma unroll
-    for (int j = 0; j < 10; j++) {
-        const double re = __shfl_sync(full, r.re, j), im = __shfl_sync(full, r.im, j);
-        if (j < N) st.r[j] = {re, im};
-    }
-    st.floor_md = floor_md;
-    st.stalled = stalled;
-    st.iter = iter;
-    st.done = (done || iter >= 300) ? 1 : 0;
-}
-#endif
 
 // Term tables of OpenCV's two GENERATED straight-line blocks (getCoeffMat, det B(z)): one copy for the host build of
 // this header (tests/host_harness) and one in constant memory for the kernels (every thread of a warp walks the table

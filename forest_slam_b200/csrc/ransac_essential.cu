@@ -65,15 +65,14 @@ struct EPolicy {
         for (int c = 0; c < 4; c++)
             for (int i = threadIdx.x; i < n; i += blockDim.x) dst[c * prm.n_max + i] = src[c * prm.n_max + i];
     }
-    // Durand-Kerner sweeps a solve may spend in the one-thread-per-iteration pass.  Converging polynomials need 15-45;
-    // about one in 4000 (a near-double root) never settles and OpenCV runs its full 300 sweeps on it — those are
-    // suspended and finished by a whole warp (cvm::dk_advance_warp) instead of stalling the round behind one thread.
-    static constexpr int DK_BUDGET = 48;
-    static constexpr bool HAS_TAIL = true;
+    // cv::solvePoly runs 300 Durand-Kerner sweeps on every polynomial and the bits it returns are those of sweep 300
+    // (fivepoint.cuh: dk_stop_rule), so every solve runs them all: ~480k dependent-ish fp64 operations per thread, the
+    // bulk of the solver.  One warp per SM sub-partition is both the latency and the fp64-issue optimum (a sweep's
+    // critical path of ~420 dependent operations keeps the pipe ~3/4 busy from one warp), so no solve is deferred.
+    static constexpr int DK_BUDGET = 300;
+    static constexpr bool HAS_TAIL = false;
     struct Tail {
         int slot, pad;
-        cvm::FPSetup fs;
-        cvm::DKState dk;
     };
     static constexpr int SOLVE_THREADS = 64;
     static constexpr int SOLVE_SMEM_DOUBLES = 0;  // the five-point solver keeps its state in registers / local memory
@@ -91,37 +90,11 @@ struct EPolicy {
         }
         cvm::FPSetup fs;
         if (!cvm::five_point_setup(q1, q2, fs)) return 0;
-        cvm::DKState dk;
-        cvm::dk_init(fs.coeffs, dk);
-        cvm::dk_advance(fs.coeffs, dk, DK_BUDGET);
-        if (!dk.done) {
-            const int t = atomicAdd(n_tail, 1);
-            if (t < rg::TAIL_CAP) {
-                tail[t].slot = slot;
-                tail[t].fs = fs;
-                tail[t].dk = dk;
-                return -1;
-            }
-            cvm::dk_advance(fs.coeffs, dk, 300);
-        }
         cvm::Cplx roots[10];
-        const int n = cvm::dk_finish(dk, roots);
+        const int n = cvm::dk_solve(fs.coeffs, roots, DK_BUDGET);
         return cvm::five_point_models(fs, roots, n, models);
     }
-    __device__ static int solve_tail(const Params&, Tail& T, double* models) {
-        cvm::DKState dk = T.dk;
-        double coeffs[11];
-#pragma unroll
-        for (int k = 0; k < 11; k++) coeffs[k] = T.fs.coeffs[k];
-        cvm::dk_advance_warp(coeffs, dk, 300);
-        int nm = 0;
-        if ((threadIdx.x & 31) == 0) {
-            cvm::Cplx roots[10];
-            const int n = cvm::dk_finish(dk, roots);
-            nm = cvm::five_point_models(T.fs, roots, n, models);
-        }
-        return nm;
-    }
+    __device__ static int solve_tail(const Params&, Tail&, double*) { return 0; }
     struct Scorer {
         double E[9];
         __device__ Scorer(const Params&, const double* m) {

@@ -298,7 +298,7 @@ def test_loop_closure_all_pairs(fsb):
     bank = seq.FrameBank.from_numpy(kp, counts, desc_bin=dbin)
     rec = seq.gather_loop_records(seq.loop_closure_pairs(bank, min_matches=30, chunk=8), 7).cpu().numpy()
     assert rec.shape == (21, 5)
-    n_verified = n_exact = 0
+    n_verified = 0
     for lin, a, b, nm, ni in rec:
         fa, fb = frames[a], frames[b]
         q, t, _ = lit.bf_hamming_match(fa.desc_bin, fb.desc_bin)
@@ -306,13 +306,11 @@ def test_loop_closure_all_pairs(fsb):
         if nm > 30:
             E, mask = cv2.findEssentialMat(fa.kpts[q], fb.kpts[t], focal=util.FOCAL, pp=util.PP, method=cv2.RANSAC,
                                            prob=0.999, threshold=1.0)
-            # exact except on the pinned ill-conditioned pair (tests/test_oracle_cpu.py::test_normalisation_is_fma)
-            n_exact += int(ni == int(mask.sum()))
-            assert abs(ni - int(mask.sum())) <= 2
+            assert ni == int(mask.sum())   # includes the ill-conditioned pair (0, 6) pinned in tests/golden
             n_verified += 1
         else:
             assert ni == -1
-    assert n_verified >= 6 and n_exact >= n_verified - 1
+    assert n_verified >= 6
 
 
 def test_survey_8b_names(fsb):
