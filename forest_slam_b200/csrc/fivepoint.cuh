@@ -199,11 +199,11 @@ CVM_HD int dk_solve(const double* coeffs, Cplx* roots, int max_iters = 300) {
 // this header (tests/host_harness) and one in constant memory for the kernels (every thread of a warp walks the table
 // in lock-step, so the reads are broadcasts).
 #define FS_TABLE_END };
-#define FS_TABLE_BEGIN(T, name, n) static const T name##_h[n] = {
+#define FS_TABLE_BEGIN(T, name, n) alignas(8) static const T name##_h[n] = {
 #include "fivepoint_cv_tables.inc"
 #undef FS_TABLE_BEGIN
 #ifdef __CUDACC__
-#define FS_TABLE_BEGIN(T, name, n) static __constant__ T name##_d[n] = {
+#define FS_TABLE_BEGIN(T, name, n) alignas(8) static __constant__ T name##_d[n] = {
 #include "fivepoint_cv_tables.inc"
 #undef FS_TABLE_BEGIN
 #endif
@@ -222,17 +222,33 @@ struct FPSetup {
 };
 
 // One output of a term table: fold(+/-) of left-associated products, in the order the cv2 binary evaluates them.
-// NF = factors per term slot (4 for getCoeffMat, 3 for det B(z)); 255 = factor absent; bit 7 of f0 = subtract.
+// Branch-free: absent factors are the table's 1.0 leaf (x * 1.0 == x exactly), a subtracted term is added negated
+// (a - p == a + (-p) exactly), the first term starts the sum.  NF = bytes per term (4: getCoeffMat, 3: det B(z)).
 template <int NF>
 CVM_HD double fp_eval_terms(const unsigned char* t, int n_terms, const double* L) {
+    // products in batches of 8 (independent table reads, leaf reads and multiplies in flight together), then the
+    // batch is folded into the sum in table order: the only serial chain is one add per term
+    constexpr int B = 8;
     double acc = 0;
-    for (int i = 0; i < n_terms; i++, t += NF) {
-        const int f0 = t[0];
-        double p = L[f0 & 127] * L[t[1]];
-        if (t[2] != 255) p = p * L[t[2]];
-        if (NF == 4 && t[NF - 1] != 255) p = p * L[t[NF - 1]];
-        if (i == 0) acc = (f0 & 128) ? -p : p;
-        else acc = (f0 & 128) ? acc - p : acc + p;
+    for (int i = 0; i < n_terms; i += B) {
+        double p[B];
+#pragma unroll
+        for (int u = 0; u < B; u++) {
+            const int ii = i + u < n_terms ? i + u : n_terms - 1;
+            int f0, f1, f2, f3 = 0;
+            if (NF == 4) {
+                const unsigned int w = reinterpret_cast<const unsigned int*>(t)[ii];  // terms are 4-byte aligned
+                f0 = w & 255; f1 = (w >> 8) & 255; f2 = (w >> 16) & 255; f3 = w >> 24;
+            } else {
+                f0 = t[3 * ii]; f1 = t[3 * ii + 1]; f2 = t[3 * ii + 2];
+            }
+            double q = (L[f0 & 127] * L[f1]) * L[f2];
+            if (NF == 4) q = q * L[f3];
+            p[u] = (f0 & 128) ? -q : q;
+        }
+#pragma unroll
+        for (int u = 0; u < B; u++)
+            if (i + u < n_terms) acc = (i + u == 0) ? p[u] : acc + p[u];
     }
     return acc;
 }
@@ -259,14 +275,14 @@ CVM_HD bool five_point_setup(const double (*q1)[2], const double (*q2)[2], FPSet
     //    e[], e[]^2, e[]^3 exactly as OpenCV's generated code sums them
     double A[10][20];
     {
-        double L[108 + 4];
+        double L[108 + 5];
         for (int k = 0; k < 36; k++) {
             const double e = EE[k], e2 = e * e;
             L[k] = e;
             L[36 + k] = e2;
             L[72 + k] = e2 * e;
         }
-        for (int k = 0; k < 4; k++) L[108 + k] = FP_TAB(FP_COEF_CONST)[k];
+        for (int k = 0; k < 5; k++) L[108 + k] = FP_TAB(FP_COEF_CONST)[k];
         // getCoeffMat ends by permuting its columns (left block of the system = computed columns
         // 6 8 18 15 12 5 14 7 4 11, right block = 19 13 1 16 17 3 10 9 2 0)
         for (int r = 0; r < 10; r++)

@@ -155,6 +155,34 @@ def make_sequence(n_frames: int, n_kpts: int, seed: int = SEED0, world: Optional
     return [observe(world, poses[i], n_kpts, seed + i, **kw) for i in range(n_frames)]
 
 
+def make_loop_trajectory(n_frames: int, seed: int = SEED0, laps: float = 2.0, radius: float = 25.0,
+                         centre=(0.0, 40.0)) -> List[np.ndarray]:
+    """Keyframe poses of a loop-closure job (BASELINE config 5): `laps` laps of a circle inside the forest, heading
+    along the tangent, pitch/roll noise 0.002 rad — every place is revisited one lap later."""
+    rng = np.random.default_rng(seed + 11)
+    poses = []
+    for i in range(n_frames):
+        a = 2 * np.pi * laps * i / n_frames
+        p = np.array([centre[0] + radius * np.sin(a), 0.0, centre[1] - radius * np.cos(a)])
+        yaw = a + np.pi / 2      # tangent: d/da (sin a, -cos a) = (cos a, sin a) = rot_y(yaw) e_z with yaw = pi/2 - ... see below
+        # rot_y(yaw) e_z = (sin yaw, 0, cos yaw); the tangent is (cos a, 0, sin a) = (sin(pi/2 - a), 0, cos(pi/2 - a))
+        yaw = np.pi / 2 - a
+        R = _rot_y(yaw) @ _rot_x(rng.normal(0, 0.002)) @ _rot_z(rng.normal(0, 0.002))
+        T = np.eye(4)
+        T[:3, :3] = R
+        T[:3, 3] = p
+        poses.append(T)
+    return poses
+
+
+def make_loop_sequence(n_frames: int, n_kpts: int, seed: int = SEED0, world: Optional[ForestWorld] = None,
+                       **kw) -> List[Frame]:
+    """`n_frames` keyframes along make_loop_trajectory (binary + float descriptors, as make_sequence)."""
+    world = world or make_world(seed)
+    poses = make_loop_trajectory(n_frames, seed)
+    return [observe(world, poses[i], n_kpts, seed + 50000 + i, **kw) for i in range(n_frames)]
+
+
 def relative_pose(f0: Frame, f1: Frame):
     """(R, t) with X_cam1 = R X_cam0 + t — what recoverPose / solvePnP estimate for the pair (f0, f1)."""
     T = np.linalg.inv(f1.T_wc) @ f0.T_wc

@@ -43,7 +43,7 @@ int main() {
     double *q, *models; int* cnt; long long* cyc;
     cudaMalloc(&q, h.size() * 8); cudaMemcpy(q, h.data(), h.size() * 8, cudaMemcpyHostToDevice);
     cudaMalloc(&models, (size_t)NS * 90 * 8); cudaMalloc(&cnt, NS * 4); cudaMalloc(&cyc, NS * 8);
-    for (int lanes_ : {1000, 8}) {
+    for (int lanes_ : {1000, 8, 32}) {
         int lanes = lanes_;
         const bool single = lanes == 1000;
         if (single) lanes = 1;
