@@ -807,14 +807,14 @@ def run_pnp_sweep(args, ctx: Ctx):
     b = a + 1
     m = api.hamming_match_batch(bank.desc_bin, bank.counts, a, b, cross_check=True, want_matches1=False)
     g = api.gather_matches_batch(bank.kpts, bank.counts, a, b, m["matches0"])
-    dsp = torch.gather(bank.disparity.index_select(0, a.long()), 1, g["src_idx"].clamp(0, n - 1).long())
     cam = api.ForestCamera()
     K = float(g["n_corr"].float().mean())
     sweep = []
     fp64_peak = float(ctx.peaks["pipes"]["fp64_tflops_no_fma"])
     for H in (1000, 2000, 4000, 8000, 16000, 32000, 64000):
         def fn():
-            bp = api.backproject_filter_batch(g["mkpts0"], g["mkpts1"], dsp, g["n_corr"], camera=cam)
+            bp = api.backproject_filter_bank(g["mkpts0"], g["mkpts1"], g["n_corr"], bank.disparity, a, g["src_idx"],
+                                             camera=cam)
             return api.solve_pnp_ransac_batch(bp["points3d"], bp["pts2d"], bp["n_out"], camera=cam, reproj_error=1.0,
                                               confidence=1.0, max_iters=H, min_points=6), bp
         s, bp = fn()
@@ -854,7 +854,8 @@ def run_pnp_sweep(args, ctx: Ctx):
     if not args.no_verify:
         # parity at H = 1000 with the reference's own arguments (confidence 0.99: adaptive semantics)
         from oracle import cv_literal as lit
-        bp = api.backproject_filter_batch(g["mkpts0"], g["mkpts1"], dsp, g["n_corr"], camera=cam)
+        bp = api.backproject_filter_bank(g["mkpts0"], g["mkpts1"], g["n_corr"], bank.disparity, a, g["src_idx"],
+                                         camera=cam)
         s = api.solve_pnp_ransac_batch(bp["points3d"], bp["pts2d"], bp["n_out"], camera=cam, min_points=6)
         bad = 0
         for i in range(P):

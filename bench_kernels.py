@@ -5,8 +5,8 @@ Not the contract bench (that is bench.py); this answers BASELINE.json's "each ch
 for the Hamming, scoring and triangulation kernels against B200 peak" with one JSON line per kernel:
   {"kernel", "config", "ms", "algorithmic": {...work figures of DESIGN.md §4...}, "bound", "achieved", "peak", "frac"}
 Timing: CUDA events on the launching stream, 3 warm-ups, median of `--reps`, a 256 MB write between launches (L2 flush).
-Peaks: MEASURED_PEAKS.json (HBM, bf16 tensor) when present; CUDA-core pipe peaks are nominal figures computed from
-148 SMs x lanes x the SM clock nvidia-smi reports (stated per line).
+Peaks: MEASURED_PEAKS.json (HBM, bf16 tensor) when present; CUDA-core pipe peaks (fp64 without FMA, popc, MUFU ex2) are
+the measured rates in profiles/pipe_peaks.json (scratch/pipe_peaks.cu run on a B200 of this pool).
 """
 from __future__ import annotations
 
@@ -55,6 +55,17 @@ def peaks():
         except Exception:
             pass
     return p
+
+
+def pipe_peaks():
+    """Measured CUDA-core pipe rates (profiles/pipe_peaks.json, scratch/pipe_peaks.cu on a B200 of this pool)."""
+    path = os.path.join(ROOT, "profiles", "pipe_peaks.json")
+    if os.path.exists(path):
+        j = json.load(open(path))
+        j["source"] = "measured (profiles/pipe_peaks.json)"
+        return j
+    return {"fp64_tflops_no_fma": 18.6, "fp64_tflops_fma": 37.2, "popc_gops": 4653.0, "ex2_gops": 4653.0,
+            "source": "nominal (148 SMs x lanes x 1.965 GHz)"}
 
 
 def sm_clock_ghz() -> float:
@@ -108,6 +119,7 @@ def main():
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     pk = peaks()
+    pp = pipe_peaks()
     ghz = sm_clock_ghz()
     T = Timer(args.reps)
     P = args.pairs
@@ -117,7 +129,8 @@ def main():
     def on(name):
         return want is None or name in want
 
-    print(json.dumps({"peaks": pk, "sm_clock_ghz": ghz, "sms": SMS, "device": torch.cuda.get_device_name(0)}))
+    print(json.dumps({"peaks": pk, "pipe_peaks": pp, "sm_clock_ghz": ghz, "sms": SMS,
+                      "device": torch.cuda.get_device_name(0)}))
 
     # ------------------------------------------------------------------ A2 Hamming (POPC pipe; HBM figure asked too)
     if on("hamming"):
@@ -130,7 +143,7 @@ def main():
             ms = T(lambda: fsb.hamming_match_batch(desc, counts, a, b, popc=True))
             popc = P * n * n * 8.0
             byts = P * ((n + n) * 32 + n * 12.0)
-            peak_popc = SMS * 16 * ghz  # G popc32/s at 16 lanes/clk/SM (CUDA programming guide throughput table)
+            peak_popc = pp["popc_gops"]  # measured G popc32/s (16 lanes/clk/SM)
             line("k_hamming_top2 (+finalize)", {"pairs": P, "n0": n, "n1": n, "crossCheck": True}, ms,
                  {"popc32": popc, "bytes": byts, "hbm_gbs": byts / ms / 1e6}, "popc pipe",
                  popc / ms / 1e6, peak_popc, "Gpopc32/s",
@@ -223,7 +236,7 @@ def main():
         P3 = rng.uniform([-10, -3, 2], [10, 3, 40], (Pn, K, 3)).astype(np.float32)
         nc = torch.full((Pn,), K, dtype=torch.int32, device=dev)
         x0t, x1t, P3t = (torch.from_numpy(v).to(dev) for v in (x0, x1, P3))
-        fp64_peak = SMS * 64 * 2 * ghz / 1e3  # TFLOP/s: 64 DFMA lanes/clk/SM nominal (B200)
+        fp64_peak = pp["fp64_tflops_no_fma"]  # measured DMUL + DADD rate (the scorers run without FMA contraction)
         for H in (1024, 2048, 4096, 8192, 16384, 32768, 65536):
             E = torch.from_numpy(rng.normal(0, 1, (Pn, H, 3, 3))).to(dev)
             ms = T(lambda: fsb.score_essential_batch(x0t, x1t, nc, E, focal=cam.fx, pp=(cam.cx, cam.cy)))
@@ -268,7 +281,7 @@ def main():
             ms = T(lambda: fsb.sinkhorn_match_batch(sc, cm, cn, iters=iters))
             ex2 = pp * m * n * 2.0 * iters
             byts = pp * m * n * 4.0
-            peak_mufu = SMS * 16 * ghz  # G ex2/s at 16 MUFU lanes/clk/SM
+            peak_mufu = pp["ex2_gops"]  # measured G ex2/s (16 MUFU lanes/clk/SM)
             line("k_sk_resident (cooperative, 1 launch per group)", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms,
                  {"ex2": ex2, "bytes_hbm_once": byts, "bytes_streamed": byts * (iters + 1),
                   "stream_gbs": byts * (iters + 1) / ms / 1e6, "pairs_per_s": pp / ms * 1e3}, "mufu pipe",

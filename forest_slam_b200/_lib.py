@@ -60,6 +60,11 @@ SIGNATURES = {
                                         C.c_double, C.c_double, C.c_double, ptr, ptr, ptr]),
     "fs_backproject_filter": (C.c_int, [ptr, ptr, ptr, ptr, C.c_int, C.c_int, C.POINTER(FSCamera),
                                         C.c_double, C.c_double, C.c_double, ptr, ptr, ptr, ptr]),
+    "fs_backproject_filter_bank": (C.c_int, [ptr, ptr, ptr, C.c_int, C.c_int, ptr, C.c_int, C.c_int, C.c_int, ptr, ptr,
+                                             C.POINTER(FSCamera), C.c_double, C.c_double, C.c_double, ptr, ptr, ptr,
+                                             ptr]),
+    "fs_filter_matches_distance": (C.c_int, [ptr, ptr, C.c_int, C.c_int, C.c_int, ptr, ptr]),
+    "fs_pack_records": (C.c_int, [ptr, ptr, ptr, ptr, ptr, ptr, ptr, C.c_int, ptr, ptr]),
     "fs_find_essential_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "fs_find_essential_ransac": (C.c_int, [ptr, ptr, ptr, C.c_int, C.c_int, C.c_double, C.c_double,
                                            C.c_double, C.c_double, C.c_double, C.c_int, ptr, ptr, ptr, ptr,

@@ -456,6 +456,67 @@ def backproject_filter_batch(mkpts0, mkpts1, disparity, n_corr, *, camera: Fores
     return {"points3d": p3, "pts2d": p2, "n_out": no}
 
 
+def backproject_filter_bank(mkpts0, mkpts1, n_corr, disparity, pair_a, src_idx=None, *,
+                            camera: ForestCamera = ForestCamera(), baseline: Optional[float] = None,
+                            zmin: float = 0.1, zmax: float = 1000.0):
+    """A6 over a frame bank with the reference's lookup (stereo_slam.py:274-289): ``disparity`` is the per-keypoint
+    bank [F, n_max] (needs ``src_idx`` from gather_matches_batch) or the frames' dense maps [F, H, W] (looked up at
+    (int(y), int(x)) of the previous-left keypoint) → dict(points3d, pts2d, n_out)."""
+    lib = _lib.load()
+    mkpts0 = _chk(mkpts0, torch.float32, "mkpts0")
+    mkpts1 = _chk(mkpts1, torch.float32, "mkpts1")
+    disparity = _chk(disparity, torch.float32, "disparity")
+    n_corr = _chk(n_corr, torch.int32, "n_corr")
+    dev = mkpts0.device
+    P, n_max = int(mkpts0.shape[0]), int(mkpts0.shape[1])
+    pa = _chk(_to_cuda(pair_a, torch.int32, dev), torch.int32, "pair_a")
+    dense = disparity.dim() == 3
+    if dense:
+        F, H, W = (int(x) for x in disparity.shape)
+    else:
+        if src_idx is None:
+            raise ValueError("per-keypoint disparity needs src_idx (gather_matches_batch)")
+        if int(disparity.shape[1]) != n_max:
+            raise ValueError("disparity must be [n_frames, n_max]")
+        src_idx = _chk(src_idx, torch.int32, "src_idx")
+        F, H, W = int(disparity.shape[0]), 0, 0
+    p3 = torch.empty((P, n_max, 3), dtype=torch.float32, device=dev)  # rows >= n_out[p] are never read
+    p2 = torch.empty((P, n_max, 2), dtype=torch.float32, device=dev)
+    no = torch.empty((P,), dtype=torch.int32, device=dev)
+    cam = camera.as_struct()
+    B = camera.baseline if baseline is None else float(baseline)
+    _lib.check(lib.fs_backproject_filter_bank(_p(mkpts0), _p(mkpts1), _p(n_corr), P, n_max, _p(disparity), F, H, W,
+                                              _p(pa), _p(src_idx), C.byref(cam), B, zmin, zmax, _p(p3), _p(p2),
+                                              _p(no), _stream()), "fs_backproject_filter_bank")
+    return {"points3d": p3, "pts2d": p2, "n_out": no}
+
+
+def filter_matches_distance(matches0: torch.Tensor, dist0: torch.Tensor, max_distance: int) -> torch.Tensor:
+    """In place: matches0[p, q] = -1 where dist0[p, q] > max_distance (ORBmatcher.cc:704 style gate) → n_matches [P]."""
+    lib = _lib.load()
+    matches0 = _chk(matches0, torch.int32, "matches0")
+    dist0 = _chk(dist0, torch.int32, "dist0")
+    P, n_max = int(matches0.shape[0]), int(matches0.shape[1])
+    nm = torch.empty((P,), dtype=torch.int32, device=matches0.device)
+    _lib.check(lib.fs_filter_matches_distance(_p(matches0), _p(dist0), P, n_max, int(max_distance), _p(nm), _stream()),
+               "fs_filter_matches_distance")
+    return nm
+
+
+def pack_records(n_matches, n_inliers, status, R, t, n_good=None, iters=None) -> torch.Tensor:
+    """[P, 20] f64 per-pair result records (n_matches, n_inliers, status, n_good, R, t, iters) for the one gather."""
+    lib = _lib.load()
+    R = _chk(R, torch.float64, "R")
+    t = _chk(t, torch.float64, "t")
+    P = int(R.shape[0])
+    i32 = lambda x, n: None if x is None else _chk(x, torch.int32, n)
+    rec = torch.empty((P, 20), dtype=torch.float64, device=R.device)
+    _lib.check(lib.fs_pack_records(_p(i32(n_matches, "n_matches")), _p(i32(n_inliers, "n_inliers")),
+                                   _p(i32(status, "status")), _p(i32(n_good, "n_good")), _p(R), _p(t),
+                                   _p(i32(iters, "iters")), P, _p(rec), _stream()), "fs_pack_records")
+    return rec
+
+
 # ------------------------------------------------------------------------------------------- A4 / A5
 def find_essential_batch(mkpts0, mkpts1, n_corr, *, focal: float, pp: Tuple[float, float], prob: float = 0.999,
                          threshold: float = 1.0, max_iters: int = 1000):

@@ -172,9 +172,13 @@ __global__ void k_rodrigues(const double* __restrict__ rvec, int n, double* __re
 
 // T_cum[k] = T_init * T_0 * ... * T_k  (mono_slam.py:118, stereo_slam.py:306); a prefix product is
 // sequential by definition: 16 lanes of one warp each own one element of the running 4x4.
+struct Pose16 {
+    double m[16];
+};
 __global__ void k_compose(const double* __restrict__ R, const double* __restrict__ t,
-                          const int32_t* __restrict__ status, int n, const double* T0, double* T_cum) {
-    // T0 aliases T_cum[0..15] (the initial pose travels through the first output slot)
+                          const int32_t* __restrict__ status, int n, const Pose16 T0v, double* T_cum) {
+    // the initial pose travels BY VALUE in the kernel arguments: no host buffer outlives the call (graph-capture safe)
+    const double* T0 = T0v.m;
     __shared__ double s_T[16];
     __shared__ double s_M[16];
     const int e = threadIdx.x;  // 0..15
@@ -223,6 +227,97 @@ k_transform_points(const float* __restrict__ pts, const int32_t* __restrict__ n_
         d[1] = (float)(M[4] * x + M[5] * y + M[6] * z + M[7]);
         d[2] = (float)(M[8] * x + M[9] * y + M[10] * z + M[11]);
     }
+}
+
+// A6 over a frame bank: the disparity of correspondence i of pair p is looked up where the reference looks it up —
+// per-keypoint (synthetic: disparity[frame][query index]) or in the frame's dense map at (int(y), int(x))
+// (stereo_slam.py:274-281) — then back-projected and filtered jointly with the partner points (:288-289).
+__global__ void __launch_bounds__(256)
+k_backproject_filter_bank(const float2* __restrict__ mk0, const float2* __restrict__ mk1,
+                          const int32_t* __restrict__ n_corr, int n_max, const float* __restrict__ disparity,
+                          int per_frame, int map_h, int map_w, const int32_t* __restrict__ pair_a,
+                          const int32_t* __restrict__ src_idx, BackprojConst k, float* __restrict__ p3,
+                          float2* __restrict__ p2, int32_t* __restrict__ n_out) {
+    __shared__ int s_warp[33];
+    const int p = blockIdx.x;
+    const int n = min(n_corr[p], n_max);
+    const size_t o = (size_t)p * n_max;
+    const float* dmap = disparity + (size_t)pair_a[p] * per_frame;
+    int base = 0;
+    for (int i0 = 0; i0 < n; i0 += blockDim.x) {
+        const int i = i0 + threadIdx.x;
+        float X = 0, Y = 0, Z = 0;
+        bool ok = false;
+        float2 partner = make_float2(0.f, 0.f);
+        if (i < n) {
+            const float2 xy = mk0[o + i];
+            float d;
+            if (map_h > 0) {
+                int ix = (int)xy.x, iy = (int)xy.y;
+                const bool inside = ix >= 0 && ix < map_w && iy >= 0 && iy < map_h;
+                ix = min(max(ix, 0), map_w - 1);
+                iy = min(max(iy, 0), map_h - 1);
+                d = inside ? dmap[(size_t)iy * map_w + ix] : 0.0f;
+            } else {
+                d = dmap[min(max(src_idx[o + i], 0), n_max - 1)];
+            }
+            ok = backproject_one(xy.x, xy.y, d, k, X, Y, Z);
+            partner = mk1[o + i];
+        }
+        int total;
+        const int off = block_compact(ok, total, s_warp);
+        if (ok) {
+            float* dst = p3 + 3 * (o + base + off);
+            dst[0] = X;
+            dst[1] = Y;
+            dst[2] = Z;
+            p2[o + base + off] = partner;
+        }
+        base += total;
+    }
+    if (threadIdx.x == 0) n_out[p] = base;
+}
+
+// matches whose descriptor distance exceeds max_distance are dropped (ORB_SLAM3/src/ORBmatcher.cc:704 `bestDist <= TH_LOW`
+// style gate; the loop-closure driver counts only such matches) and the pair's match count is recomputed.
+__global__ void __launch_bounds__(256)
+k_filter_matches_distance(int32_t* __restrict__ matches0, const int32_t* __restrict__ dist0, int n_max, int max_distance,
+                          int32_t* __restrict__ n_matches) {
+    __shared__ int s_cnt;
+    const int p = blockIdx.x;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    int c = 0;
+    for (int i = threadIdx.x; i < n_max; i += blockDim.x) {
+        const size_t o = (size_t)p * n_max + i;
+        int m = matches0[o];
+        if (m >= 0 && dist0[o] > max_distance) matches0[o] = m = -1;
+        c += m >= 0;
+    }
+    c = __reduce_add_sync(0xffffffffu, c);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&s_cnt, c);
+    __syncthreads();
+    if (threadIdx.x == 0) n_matches[p] = s_cnt;
+}
+
+// the fixed-size per-pair result record of the one gather (sequence.py RECORD_F64 = 20 doubles):
+// n_matches, n_inliers, status, n_good, R[9], t[3], iters, pad[3]
+__global__ void k_pack_records(const int32_t* __restrict__ n_matches, const int32_t* __restrict__ n_inliers,
+                               const int32_t* __restrict__ status, const int32_t* __restrict__ n_good,
+                               const double* __restrict__ R, const double* __restrict__ t,
+                               const int32_t* __restrict__ iters, int n, double* __restrict__ rec) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n * 20) return;
+    const int p = i / 20, f = i % 20;
+    double v = 0.0;
+    if (f == 0) v = n_matches[p];
+    else if (f == 1) v = n_inliers[p];
+    else if (f == 2) v = status[p];
+    else if (f == 3) v = n_good ? n_good[p] : 0;
+    else if (f < 13) v = R[9 * (size_t)p + f - 4];
+    else if (f < 16) v = t[3 * (size_t)p + f - 13];
+    else if (f == 16) v = iters ? iters[p] : 0;
+    rec[i] = v;
 }
 
 BackprojConst make_bp(const FSCamera* cam, double baseline, double zmin, double zmax) {
@@ -287,6 +382,48 @@ extern "C" int fs_backproject_filter(const float* mkpts0, const float* mkpts1, c
     return FS_OK;
 }
 
+extern "C" int fs_backproject_filter_bank(const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                                          int n_pairs, int n_max, const float* disparity, int n_frames, int map_h,
+                                          int map_w, const int32_t* pair_a, const int32_t* src_idx,
+                                          const FSCamera* cam, double baseline, double z_min, double z_max,
+                                          float* points3d_out, float* pts2d_out, int32_t* n_out,
+                                          fs_stream_t stream) {
+    FS_REQUIRE(n_pairs >= 0 && n_max >= 0 && n_frames >= 0 && map_h >= 0 && map_w >= 0, "negative size");
+    if (n_pairs == 0) return FS_OK;
+    FS_REQUIRE(mkpts0 && mkpts1 && disparity && n_corr && pair_a && cam && points3d_out && pts2d_out && n_out,
+               "null pointer");
+    FS_REQUIRE(map_h > 0 ? map_w > 0 : src_idx != nullptr, "dense maps need map_w, per-keypoint disparity needs src_idx");
+    const int per_frame = map_h > 0 ? map_h * map_w : n_max;
+    k_backproject_filter_bank<<<n_pairs, 256, 0, (cudaStream_t)stream>>>(
+        (const float2*)mkpts0, (const float2*)mkpts1, n_corr, n_max, disparity, per_frame, map_h, map_w, pair_a,
+        src_idx, make_bp(cam, baseline, z_min, z_max), points3d_out, (float2*)pts2d_out, n_out);
+    FS_LAUNCH_CHECK("k_backproject_filter_bank");
+    return FS_OK;
+}
+
+extern "C" int fs_filter_matches_distance(int32_t* matches0, const int32_t* dist0, int n_pairs, int n_max,
+                                          int max_distance, int32_t* n_matches, fs_stream_t stream) {
+    FS_REQUIRE(n_pairs >= 0 && n_max >= 0, "negative size");
+    if (n_pairs == 0) return FS_OK;
+    FS_REQUIRE(matches0 && dist0 && n_matches, "null pointer");
+    k_filter_matches_distance<<<n_pairs, 256, 0, (cudaStream_t)stream>>>(matches0, dist0, n_max, max_distance,
+                                                                         n_matches);
+    FS_LAUNCH_CHECK("k_filter_matches_distance");
+    return FS_OK;
+}
+
+extern "C" int fs_pack_records(const int32_t* n_matches, const int32_t* n_inliers, const int32_t* status,
+                               const int32_t* n_good, const double* R, const double* t, const int32_t* iters,
+                               int n_pairs, double* records, fs_stream_t stream) {
+    FS_REQUIRE(n_pairs >= 0, "negative size");
+    if (n_pairs == 0) return FS_OK;
+    FS_REQUIRE(n_matches && n_inliers && status && R && t && records, "null pointer");
+    k_pack_records<<<(n_pairs * 20 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(n_matches, n_inliers, status, n_good,
+                                                                                 R, t, iters, n_pairs, records);
+    FS_LAUNCH_CHECK("k_pack_records");
+    return FS_OK;
+}
+
 extern "C" int fs_rodrigues(const double* rvec, int n, double* R, fs_stream_t stream) {
     FS_REQUIRE(n >= 0, "negative size");
     if (n == 0) return FS_OK;
@@ -301,11 +438,9 @@ extern "C" int fs_compose_trajectory(const double* R, const double* t, const int
     FS_REQUIRE(n >= 0, "negative size");
     if (n == 0) return FS_OK;
     FS_REQUIRE(R && t && T_cum, "null pointer");
-    // T_init travels through the first output slot to avoid a device allocation
-    double T0[16] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
-    if (T_init_host) memcpy(T0, T_init_host, sizeof(T0));
-    FS_CUDA(cudaMemcpyAsync(T_cum, T0, sizeof(T0), cudaMemcpyHostToDevice, (cudaStream_t)stream));
-    k_compose<<<1, 32, 0, (cudaStream_t)stream>>>(R, t, status, n, T_cum, T_cum);
+    Pose16 T0 = {{1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1}};
+    if (T_init_host) memcpy(T0.m, T_init_host, sizeof(T0.m));
+    k_compose<<<1, 32, 0, (cudaStream_t)stream>>>(R, t, status, n, T0, T_cum);
     FS_LAUNCH_CHECK("k_compose");
     return FS_OK;
 }

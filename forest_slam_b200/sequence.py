@@ -25,7 +25,8 @@ class FrameBank:
     counts: torch.Tensor                    # [F] i32
     desc_f32: Optional[torch.Tensor] = None  # [F, 256, n_max] f32 (SuperPoint layout)
     desc_bin: Optional[torch.Tensor] = None  # [F, n_max, 32] u8 (ORB layout)
-    disparity: Optional[torch.Tensor] = None  # [F, n_max] f32 per-keypoint disparity (uL - uR)
+    disparity: Optional[torch.Tensor] = None  # [F, n_max] f32 per-keypoint disparity (uL - uR), or the frames' dense
+    #                                           disparity maps [F, H, W] f32 (SGBM / 16, stereo_slam.py:262-271)
     operands: Optional[torch.Tensor] = None  # [F, n_max + 1, 512] fp16 operand bank (api.float_prepare) of the tensor-core matcher
 
     @staticmethod
@@ -133,11 +134,11 @@ def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary",
     pb = api._to_cuda(pair_b, torch.int32, dev)
     m = _match(bank, pa, pb, descriptor, threshold, ratio, exact_fp32, scale, timer, split3)
     g = _run(timer, "gather", lambda: api.gather_matches_batch(bank.kpts, bank.counts, pa, pb, m["matches0"]))
-    # per-correspondence disparity of the previous-left keypoint (the reference looks it up in the SGBM map)
-    P, n_max = g["src_idx"].shape
-    disp = torch.gather(bank.disparity.index_select(0, pa.long()), 1, g["src_idx"].clamp_(0, n_max - 1).long())
+    # disparity of the previous-left keypoint: looked up inside the kernel, per keypoint or in the frame's dense map
+    # at (int(y), int(x)) as the reference does (stereo_slam.py:274-281)
     b = _run(timer, "triangulate",
-             lambda: api.backproject_filter_batch(g["mkpts0"], g["mkpts1"], disp, g["n_corr"], camera=camera))
+             lambda: api.backproject_filter_bank(g["mkpts0"], g["mkpts1"], g["n_corr"], bank.disparity, pa,
+                                                 g["src_idx"], camera=camera))
     s = _run(timer, "pnp_ransac",
              lambda: api.solve_pnp_ransac_batch(b["points3d"], b["pts2d"], b["n_out"], camera=camera,
                                                 reproj_error=reproj_error, confidence=confidence, max_iters=max_iters,
@@ -150,18 +151,11 @@ def stereo_pairs(bank: FrameBank, pair_a, pair_b, *, descriptor: str = "binary",
 
 
 def pack_records(res: Dict[str, torch.Tensor]) -> torch.Tensor:
-    """Fixed-size per-pair result record [P, 20] f64: n_matches, n_inliers, status, n_good, R(9), t(3), iters, pad."""
+    """Fixed-size per-pair result record [P, 20] f64: n_matches, n_inliers, status, n_good, R(9), t(3), iters, pad
+    (one launch of k_pack_records)."""
     P = res["R"].shape[0]
-    rec = torch.zeros((P, RECORD_F64), dtype=torch.float64, device=res["R"].device)
-    rec[:, 0] = res["n_matches"].double()
-    rec[:, 1] = res["n_inliers"].double()
-    rec[:, 2] = res["status"].double()
-    if "n_good" in res:
-        rec[:, 3] = res["n_good"].double()
-    rec[:, 4:13] = res["R"].reshape(P, 9)
-    rec[:, 13:16] = res["t"].reshape(P, 3)
-    rec[:, 16] = res["iters"].double()
-    return rec
+    return api.pack_records(res["n_matches"], res["n_inliers"], res["status"], res["R"].reshape(P, 9),
+                            res["t"].reshape(P, 3), n_good=res.get("n_good"), iters=res.get("iters"))
 
 
 def gather_records(rec_local: torch.Tensor, n_pairs_total: int) -> torch.Tensor:
@@ -172,8 +166,11 @@ def gather_records(rec_local: torch.Tensor, n_pairs_total: int) -> torch.Tensor:
         return rec_local
     W = dist.get_world_size()
     per = (n_pairs_total + W - 1) // W
-    pad = torch.zeros((per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
-    pad[: rec_local.shape[0]] = rec_local
+    if rec_local.shape[0] == per:
+        pad = rec_local
+    else:
+        pad = torch.zeros((per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
+        pad[: rec_local.shape[0]] = rec_local
     out = torch.empty((W, per, rec_local.shape[1]), dtype=rec_local.dtype, device=rec_local.device)
     dist.all_gather_into_tensor(out.view(W * per, -1), pad)
     # [W, per] -> pair index i = slot * W + rank
@@ -259,12 +256,15 @@ def shard_all_pairs(n_frames: int, rank: int, world: int, block: int = 1024) -> 
     return lin[(lin // block) % world == rank]
 
 
-def loop_closure_pairs(bank: FrameBank, *, descriptor: str = "binary", min_matches: int = 30, rank: int = 0,
+def loop_closure_pairs(bank: FrameBank, *, descriptor: str = "binary", min_matches: int = 30, max_distance: int = 64,
+                       rank: int = 0,
                        world: int = 1, chunk: int = 4096, block: int = 1024, camera: ForestCamera = ForestCamera(),
                        prob: float = 0.999, ransac_threshold: float = 1.0, max_iters: int = 1000,
                        threshold: Optional[float] = None, scale: float = 1.0) -> torch.Tensor:
     """All-pairs keyframe matching: every (a, b), a < b, of the bank is matched (mutual nearest neighbour); pairs with
-    more than `min_matches` mutual matches go through essential-matrix RANSAC.  This rank's share of the pairs only.
+    more than `min_matches` mutual matches go through essential-matrix RANSAC.  Binary descriptors: a mutual match
+    counts only when its Hamming distance is <= `max_distance` (ORBmatcher.cc:704 style gate, 0 = off) — crossCheck alone
+    pairs about n/2 random descriptors of two unrelated keyframes.  This rank's share of the pairs only.
     Returns records [n_local, 5] int64 on the device: linear pair index, a, b, n_matches, n_inliers (-1: not verified)."""
     dev = bank.kpts.device
     F = int(bank.kpts.shape[0])
@@ -284,6 +284,8 @@ def loop_closure_pairs(bank: FrameBank, *, descriptor: str = "binary", min_match
         if descriptor == "binary":
             m = api.hamming_match_batch(bank.desc_bin, bank.counts, pa, pb, cross_check=True, want_matches1=False,
                                         operands=ops_bin)
+            if max_distance > 0:
+                m["n_matches"] = api.filter_matches_distance(m["matches0"], m["dist0"], max_distance)
         else:
             m = api.float_match_batch(bank.desc_f32, bank.counts, pa, pb, scale=scale, threshold=threshold,
                                       operands=operands)

@@ -241,6 +241,29 @@ int fs_backproject_filter(const float* mkpts0, const float* mkpts1, const float*
                           const FSCamera* cam_host, double baseline, double z_min, double z_max,
                           float* points3d_out, float* pts2d_out, int32_t* n_out, fs_stream_t stream);
 
+/* the same over a FRAME BANK, with the lookup the reference does (stereo_slam.py:274-281): `disparity` is either the
+ * per-keypoint bank [n_frames, n_max] f32 (map_h == 0; correspondence i of pair p reads frame pair_a[p] at query index
+ * src_idx[p, i], the index fs_gather_matches reports) or the frames' dense maps [n_frames, map_h, map_w] f32 (SGBM/16,
+ * looked up at (int(y), int(x)) of the previous-left keypoint; outside the map -> invalid). */
+int fs_backproject_filter_bank(const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                               int n_pairs, int n_max, const float* disparity, int n_frames, int map_h, int map_w,
+                               const int32_t* pair_a, const int32_t* src_idx,
+                               const FSCamera* cam_host, double baseline, double z_min, double z_max,
+                               float* points3d_out, float* pts2d_out, int32_t* n_out, fs_stream_t stream);
+
+/* distance gate on a match list (in place): matches0[p, q] = -1 where dist0[p, q] > max_distance, n_matches recounted —
+ * the `bestDist <= TH` test of ORB_SLAM3/src/ORBmatcher.cc:704; the loop-closure driver (BASELINE config 5) counts only
+ * such matches, because crossCheck alone pairs ~n/2 random descriptors of two unrelated keyframes. */
+int fs_filter_matches_distance(int32_t* matches0, const int32_t* dist0, int n_pairs, int n_max, int max_distance,
+                               int32_t* n_matches, fs_stream_t stream);
+
+/* per-pair result record of the one gather of the path: records [n_pairs, 20] f64 =
+ * n_matches, n_inliers, status, n_good (0 when NULL), R[9], t[3], iters (0 when NULL), 3 x 0 — what
+ * mono_slam.py:113-118 / stereo_slam.py:298-306 keep of a frame pair. */
+int fs_pack_records(const int32_t* n_matches, const int32_t* n_inliers, const int32_t* status,
+                    const int32_t* n_good, const double* R, const double* t, const int32_t* iters,
+                    int n_pairs, double* records, fs_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * A4  essential-matrix RANSAC — replaces
  *       E, mask = cv2.findEssentialMat(mkpts0, mkpts1, focal=K0[0,0], pp=(K0[0,2],K0[1,2]),
@@ -320,7 +343,8 @@ int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, const int32_t
  *     mono_slam.py:115-118) and the map-point transform T_cum @ [P;1] (stereo_slam.py:309-311).
  * fs_rodrigues:   rvec [n,3] f64 -> R [n,9] f64
  * fs_compose_trajectory: relative (R [n,9], t [n,3]) -> cumulative T [n,16] f64, T_k = T_0 ... T_k
- *     (sequential by definition; one warp walks the chain), skipping entries with status != 0
+ *     (sequential by definition; one warp walks the chain), skipping entries with status != 0; T_init_host (16 doubles,
+ *     NULL = identity) is read during the call and passed to the kernel by value (no host buffer outlives the call)
  * fs_transform_points: points [n_pairs, n_max, 3] f32 by T [n_pairs, 16] f64 -> out f32
  * ---------------------------------------------------------------------------------------------- */
 int fs_rodrigues(const double* rvec, int n, double* R, fs_stream_t stream);
