@@ -792,7 +792,7 @@ def run_float4096(args, ctx: Ctx):
 # ------------------------------------------------------------------------------------------------ config 4
 def run_pnp_sweep(args, ctx: Ctx):
     """BASELINE config 4: stereo back-projection + PnP RANSAC with H = 1k .. 64k hypotheses per frame pair (adaptive stop
-    disabled: confidence 1.0 keeps OpenCV's iteration cap at H, every hypothesis is solved and scored)."""
+    disabled through the C ABI's `confidence > 1` switch: every one of the H hypotheses is solved and scored)."""
     import torch
     from forest_slam_b200 import api, synth, sequence as seq
     if ctx.rank != 0:
@@ -816,7 +816,7 @@ def run_pnp_sweep(args, ctx: Ctx):
             bp = api.backproject_filter_bank(g["mkpts0"], g["mkpts1"], g["n_corr"], bank.disparity, a, g["src_idx"],
                                              camera=cam)
             return api.solve_pnp_ransac_batch(bp["points3d"], bp["pts2d"], bp["n_out"], camera=cam, reproj_error=1.0,
-                                              confidence=1.0, max_iters=H, min_points=6), bp
+                                              confidence=2.0, max_iters=H, min_points=6), bp
         s, bp = fn()
         torch.cuda.synchronize()
         ts = []
@@ -928,7 +928,7 @@ def run_loopclosure(args, ctx: Ctx):
     out = {"metric": METRIC, "value": total / t, "unit": UNIT, "n_gpus": world, "ms_per_step": 1e3 * t, "steps": 1,
            "scaling": "strong", "clocks": clk,
            "config": {"workload": "all-pairs loop-closure matching (Hamming crossCheck) + essential-matrix RANSAC "
-                                  "verification of pairs with > 30 matches", "keyframes": F, "kpts_per_frame": n,
+                                  "verification of pairs with > 30 matches (a mutual match counts when its Hamming distance is <= 64)", "keyframes": F, "kpts_per_frame": n,
                       "pairs": total, "trajectory": "two laps of a 25 m circle in the 80 m forest (synth.make_loop_sequence)",
                       "sharding": f"block-cyclic (1024 pairs) over {world} rank(s); bank replicated by one broadcast; "
                                   "one all_gather of the records"},
@@ -947,7 +947,8 @@ def run_loopclosure(args, ctx: Ctx):
         bad_m = bad_i = 0
         for j in idx:
             _, a, b, nm, ni = (int(x) for x in r[j])
-            q, tt, _ = lit.bf_hamming_match(frames[a].desc_bin, frames[b].desc_bin)
+            q, tt, d = lit.bf_hamming_match(frames[a].desc_bin, frames[b].desc_bin)
+            q, tt = q[d <= 64], tt[d <= 64]      # the job's distance gate (sequence.loop_closure_pairs max_distance)
             bad_m += int(q.size != nm)
             if nm > 30:
                 E, mask = cv2.findEssentialMat(frames[a].kpts[q], frames[b].kpts[tt], focal=lit.K0[0, 0],

@@ -189,7 +189,9 @@ k_rg_select(int round, int n_pairs, const int32_t* __restrict__ n_corr, int n_ma
                     if (c > max(best, MP - 1)) {
                         best = c;
                         if (lane < MD) S.best_model[lane] = ws.slot_models[((size_t)slot * MAXM + k) * MD + lane];
-                        nit = cvm::ransac_update_num_iters(confidence, (double)(n - c) / n, MP, nit);
+                        // confidence > 1: adaptive cap off, every one of max_iters hypotheses is solved and scored
+                        // (BASELINE config 4 sweep; cv2 has no such mode)
+                        if (confidence <= 1.0) nit = cvm::ransac_update_num_iters(confidence, (double)(n - c) / n, MP, nit);
                         last_update = it;
                     }
                 }

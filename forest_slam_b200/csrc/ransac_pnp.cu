@@ -512,7 +512,7 @@ extern "C" int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, co
     if (n_pairs == 0) return FS_OK;
     FS_REQUIRE(n_max >= 1, "n_max must be positive");
     FS_REQUIRE(points3d && pts2d && n_corr && cam && rvec && tvec && mask && n_inliers && status, "null pointer");
-    FS_REQUIRE(confidence > 0 && confidence < 1, "confidence must be in (0, 1)");
+    FS_REQUIRE(confidence > 0, "confidence must be in (0, 1], or > 1 to switch the adaptive iteration cap off");
     const size_t need = fs_solve_pnp_workspace_bytes(n_pairs, n_max, max_iters);
     if (!workspace || workspace_bytes < need) {
         fs::set_error("fs_solve_pnp_ransac: workspace %zu < %zu", workspace_bytes, need);

@@ -11,23 +11,32 @@ import numpy as np
 
 
 def quaternion_from_matrix(R: np.ndarray) -> np.ndarray:
-    """(qx, qy, qz, qw) of a rotation matrix, sign convention of tf.transformations.quaternion_from_matrix (qw >= 0
-    branch first; the largest diagonal term otherwise)."""
-    R = np.asarray(R, dtype=np.float64)[:3, :3]
-    tr = np.trace(R)
-    if tr > 0:
-        s = 2.0 * np.sqrt(tr + 1.0)
-        q = np.array([(R[2, 1] - R[1, 2]) / s, (R[0, 2] - R[2, 0]) / s, (R[1, 0] - R[0, 1]) / s, 0.25 * s])
+    """(qx, qy, qz, qw) of a rotation matrix exactly as ROS tf.transformations.quaternion_from_matrix computes it (the
+    call at mono_slam.py:127 / stereo_slam.py:327): homogeneous 4x4 with M[3,3] = 1, branch on trace(M) > M[3,3], else
+    the largest diagonal element; every component scaled by 0.5 / sqrt(t * M[3,3]); NO sign normalisation — in the
+    second branch qw can come out negative, and the reference writes it that way."""
+    M = np.eye(4)
+    M[:3, :3] = np.asarray(R, dtype=np.float64)[:3, :3]
+    q = np.empty(4)
+    t = np.trace(M)
+    if t > M[3, 3]:
+        q[3] = t
+        q[2] = M[1, 0] - M[0, 1]
+        q[1] = M[0, 2] - M[2, 0]
+        q[0] = M[2, 1] - M[1, 2]
     else:
-        i = int(np.argmax(np.diag(R)))
-        j, k = (i + 1) % 3, (i + 2) % 3
-        s = 2.0 * np.sqrt(R[i, i] - R[j, j] - R[k, k] + 1.0)
-        q = np.empty(4)
-        q[i] = 0.25 * s
-        q[j] = (R[j, i] + R[i, j]) / s
-        q[k] = (R[k, i] + R[i, k]) / s
-        q[3] = (R[k, j] - R[j, k]) / s
-    return q if q[3] >= 0 else -q
+        i, j, k = 0, 1, 2
+        if M[1, 1] > M[0, 0]:
+            i, j, k = 1, 2, 0
+        if M[2, 2] > M[i, i]:
+            i, j, k = 2, 0, 1
+        t = M[i, i] - (M[j, j] + M[k, k]) + M[3, 3]
+        q[i] = t
+        q[j] = M[i, j] + M[j, i]
+        q[k] = M[k, i] + M[i, k]
+        q[3] = M[k, j] - M[j, k]
+    q *= 0.5 / np.sqrt(t * M[3, 3])
+    return q
 
 
 def matrix_from_quaternion(q: np.ndarray) -> np.ndarray:

@@ -328,7 +328,8 @@ int fs_recover_pose(const double* E, const float* mkpts0, const float* mkpts1, c
  * points3d [n_pairs, n_max, 3] f32, pts2d [n_pairs, n_max, 2] f32, n_corr [n_pairs]
  * rvec, tvec [n_pairs, 3] f64; mask [n_pairs, n_max] u8 {0,1}; inlier_idx [n_pairs, n_max] i32
  * ascending (first n_inliers valid; may be NULL); status as above (FS_PAIR_TOO_FEW when n < min_points,
- * the reference's gate is 6).
+ * the reference's gate is 6).  confidence in (0, 1] as in cv2; a value > 1 switches the adaptive iteration cap OFF so
+ * that all max_iters hypotheses are solved and scored (BASELINE config 4 sweep; not a cv2 mode).
  * ---------------------------------------------------------------------------------------------- */
 size_t fs_solve_pnp_workspace_bytes(int n_pairs, int n_max, int max_iters);
 int fs_solve_pnp_ransac(const float* points3d, const float* pts2d, const int32_t* n_corr,

@@ -7,7 +7,7 @@ O-replay: NumPy / pure-Python restatement of the OpenCV algorithms behind the re
 The arithmetic lives in OpenCV (calib3d five-point.cpp / ptsetreg.cpp / solvepnp.cpp / epnp.cpp /
 triangulate.cpp; core rand.cpp / lapack.cpp / mathfuncs_core), which is NOT vendored under /root/reference
 (Dockerfile:62-67 clones an unpinned master).  This file restates the published algorithms; it is pinned
-against the cv2 binary of this image (opencv-python-headless 4.13.0) by tests/test_oracle_replay.py, stage
+against the cv2 binary of this image (opencv-python-headless 4.13.0) by tests/test_oracle_cpu.py, stage
 by stage (sampler, null-space basis, candidate order, masks).  The reference repo itself holds no test or
 golden vector for this path: "parity unpinned" w.r.t. the reference's own tests.
 

@@ -128,12 +128,15 @@ def test_hamming_above_4096_uses_popc_and_tc_refuses(fsb):
     gq, gt, gd = fsb.bf_match_hamming(d0, d1)
     assert np.array_equal(q, gq) and np.array_equal(t, gt) and np.array_equal(d, gd)
     ops = torch.zeros((2, 4225, 512), dtype=torch.float16, device="cuda")
-    with pytest.raises(Exception):
-        fsb.TENSOR_CORE_MATCHER, fsb.HAMMING_TC_MAX_COLS = True, 1 << 20
-        try:
-            fsb.hamming_match_batch(None, torch.tensor([10, 10], dtype=torch.int32).cuda(), [0], [1], operands=ops)
-        finally:
-            fsb.HAMMING_TC_MAX_COLS = 4096
+    from forest_slam_b200._lib import ForestSlamError
+    counts = torch.tensor([10, 10], dtype=torch.int32).cuda()
+    saved = fsb.TENSOR_CORE_MATCHER, fsb.HAMMING_TC_MAX_COLS
+    fsb.TENSOR_CORE_MATCHER, fsb.HAMMING_TC_MAX_COLS = True, 1 << 20   # make the wrapper try the tensor-core entry point
+    try:
+        with pytest.raises(ForestSlamError, match="FS_ERR_UNSUPPORTED"):
+            fsb.hamming_match_batch(None, counts, [0], [1], operands=ops)
+    finally:
+        fsb.TENSOR_CORE_MATCHER, fsb.HAMMING_TC_MAX_COLS = saved
 
 
 FLOAT_MODES = {"fp32": dict(exact_fp32=True), "split3": dict(split3=True), "top3": dict()}
@@ -149,7 +152,11 @@ def test_float_mutual_nn(fsb, n0, n1, seed, thr, ratio, mode):
     ref = lit.float_mutual_nn(d0, d1, threshold=thr, ratio=ratio)
     got = fsb.match_mutual_nn(d0, d1, threshold=thr, ratio=ratio, **FLOAT_MODES[mode])
     keep = ~ref["ambiguous0"]
-    assert keep.mean() > 0.95
+    # parity on every row the float64 oracle does not flag as a numerical tie (margin 1e-5); the number of
+    # flagged rows is bounded (seeded inputs: a handful in a thousand) and printed, not an open-ended exemption
+    n_amb = int((~keep).sum())
+    print(f"ambiguous rows: {n_amb} of {n0} (n0={n0}, n1={n1}, seed={seed}, mode={mode})")
+    assert n_amb <= max(2, n0 // 200), n_amb
     assert np.array_equal(got["matches0"][keep], ref["matches0"][keep])
     ok = ref["matches0"] >= 0
     # fp32: FMA chain; split3: split-fp16 products with the MMA's fp32 accumulation; top3: the single fp16 pass is only

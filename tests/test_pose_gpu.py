@@ -260,6 +260,57 @@ def test_stereo_sequence_driver(fsb):
         assert np.linalg.norm(res["t"][p].cpu().numpy() - ref["tvec"].ravel()) < 1e-4
 
 
+def test_stereo_sequence_driver_dense_disparity_maps(fsb):
+    """The reference looks the disparity up in the frame's dense SGBM map at (int(y), int(x)) (stereo_slam.py:274-281):
+    stereo_pairs takes [F, 600, 960] maps and gives what the literal calls give on the same maps."""
+    from forest_slam_b200 import sequence as seq, synth
+    world = synth.make_world(n_trunks=80, n_ground=2500, n_canopy=2500)
+    frames = synth.make_sequence(4, 800, world=world)
+    kp, dbin, df, disp, counts = synth.stack_frames(frames)
+    rng = np.random.default_rng(9)
+    maps = rng.uniform(2.0, 60.0, (4, 600, 960)).astype(np.float32)
+    maps[rng.random(maps.shape) < 0.02] = 0.0      # SGBM holes: 0 and -1 become 0.1 (stereo_slam.py:117-121)
+    maps[rng.random(maps.shape) < 0.02] = -1.0
+    for f in range(4):                              # the true disparity where the keypoints are
+        x, y = frames[f].kpts[:, 0].astype(int), frames[f].kpts[:, 1].astype(int)
+        maps[f, y, x] = frames[f].disparity
+    bank = seq.FrameBank.from_numpy(kp, counts, desc_bin=dbin, disparity=maps)
+    res = seq.stereo_pairs(bank, [0, 1, 2], [1, 2, 3])
+    for p in range(3):
+        a, b = frames[p], frames[p + 1]
+        q, t, _ = lit.bf_hamming_match(a.desc_bin, b.desc_bin)
+        ref = lit.stereo_pair(a.kpts[q], b.kpts[t], maps[p])
+        k = int(res["n_points"][p])
+        assert k == ref["points3D"].shape[0]
+        assert np.array_equal(res["points3d"][p, :k].cpu().numpy(), ref["points3D"])
+        assert np.array_equal(res["pts2d"][p, :k].cpu().numpy(), ref["mkpts1"])
+        ni = int(res["n_inliers"][p])
+        assert ref["ok"] and np.array_equal(res["inlier_idx"][p, :ni].cpu().numpy(), ref["inliers"].ravel())
+
+
+def test_results_independent_of_sharding(fsb):
+    """SURVEY §8(b) determinism: same bits whatever the sharding.  The pairs of a sequence are processed once in one
+    batch and once as the shards shard_pairs deals to W = 2 and W = 3 ranks (run one after the other on this GPU, each
+    through pack_records); re-interleaved, the records are bit-identical."""
+    import torch
+    from forest_slam_b200 import sequence as seq, synth
+    world = synth.make_world(n_trunks=80, n_ground=2500, n_canopy=2500)
+    frames = synth.make_sequence(8, 768, world=world)
+    kp, dbin, df, disp, counts = synth.stack_frames(frames)
+    bank = seq.FrameBank.from_numpy(kp, counts, desc_f32=df, desc_bin=dbin, disparity=disp)
+    P = 7
+    for kind in ("mono", "stereo"):
+        run = (lambda a, b: seq.mono_pairs(bank, a, b, scale=0.0625, threshold=float(np.log(0.2)))) if kind == "mono" \
+            else (lambda a, b: seq.stereo_pairs(bank, a, b))
+        full = seq.pack_records(run(list(range(P)), list(range(1, P + 1)))).cpu()
+        for W in (2, 3):
+            out = torch.empty_like(full)
+            for r in range(W):
+                idx = seq.shard_pairs(P, r, W)
+                out[idx] = seq.pack_records(run(idx.tolist(), (idx + 1).tolist())).cpu()
+            assert torch.equal(out.view(torch.int64), full.view(torch.int64)), (kind, W)
+
+
 def test_mono_sequence_driver(fsb):
     import torch
     from forest_slam_b200 import sequence as seq, synth
@@ -296,7 +347,7 @@ def test_loop_closure_all_pairs(fsb):
     frames = synth.make_sequence(7, 700, world=world)
     kp, dbin, df, disp, counts = synth.stack_frames(frames)
     bank = seq.FrameBank.from_numpy(kp, counts, desc_bin=dbin)
-    rec = seq.gather_loop_records(seq.loop_closure_pairs(bank, min_matches=30, chunk=8), 7).cpu().numpy()
+    rec = seq.gather_loop_records(seq.loop_closure_pairs(bank, min_matches=30, max_distance=0, chunk=8), 7).cpu().numpy()
     assert rec.shape == (21, 5)
     n_verified = 0
     for lin, a, b, nm, ni in rec:
@@ -311,6 +362,17 @@ def test_loop_closure_all_pairs(fsb):
         else:
             assert ni == -1
     assert n_verified >= 6
+    # with the distance gate of the loop-closure job (a mutual match counts when its Hamming distance is <= 64)
+    rec = seq.gather_loop_records(seq.loop_closure_pairs(bank, min_matches=30, max_distance=64, chunk=8), 7).cpu().numpy()
+    for lin, a, b, nm, ni in rec:
+        fa, fb = frames[a], frames[b]
+        q, t, d = lit.bf_hamming_match(fa.desc_bin, fb.desc_bin)
+        keep = d <= 64
+        assert nm == int(keep.sum())
+        if nm > 30:
+            E, mask = cv2.findEssentialMat(fa.kpts[q[keep]], fb.kpts[t[keep]], focal=util.FOCAL, pp=util.PP,
+                                           method=cv2.RANSAC, prob=0.999, threshold=1.0)
+            assert ni == int(mask.sum())
 
 
 def test_survey_8b_names(fsb):
