@@ -38,11 +38,11 @@ const char* fs_last_error_string(void) { return fs::g_err; }
 
 const char* fs_status_string(int s) {
     switch (s) {
-        case FS_OK: return "ok";
-        case FS_ERR_BAD_ARG: return "bad argument";
-        case FS_ERR_WORKSPACE: return "workspace too small";
-        case FS_ERR_CUDA: return "CUDA error";
-        case FS_ERR_UNSUPPORTED: return "unsupported device";
+        case FS_OK: return "FS_OK";
+        case FS_ERR_BAD_ARG: return "FS_ERR_BAD_ARG (bad argument)";
+        case FS_ERR_WORKSPACE: return "FS_ERR_WORKSPACE (workspace too small)";
+        case FS_ERR_CUDA: return "FS_ERR_CUDA (CUDA error)";
+        case FS_ERR_UNSUPPORTED: return "FS_ERR_UNSUPPORTED (unsupported size or device)";
         default: return "unknown status";
     }
 }

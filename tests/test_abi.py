@@ -27,7 +27,7 @@ def test_binding_table_matches_header():
     lib = _lib.load()
     assert lib.fs_version() >= 100
     assert lib.fs_status_string(0) == b"ok"
-    assert lib.fs_status_string(-2) == b"workspace too small"
+    assert lib.fs_status_string(-2) == b"FS_ERR_WORKSPACE (workspace too small)"
 
 
 def test_no_oracle_in_product():
