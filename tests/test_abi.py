@@ -26,7 +26,7 @@ def test_binding_table_matches_header():
     assert sorted(_lib.SIGNATURES) == _declared()
     lib = _lib.load()
     assert lib.fs_version() >= 100
-    assert lib.fs_status_string(0) == b"ok"
+    assert lib.fs_status_string(0) == b"FS_OK"
     assert lib.fs_status_string(-2) == b"FS_ERR_WORKSPACE (workspace too small)"
 
 
