@@ -81,6 +81,13 @@ SIGNATURES = {
     "fs_solve_pnp_ransac": (C.c_int, [ptr, ptr, ptr, C.c_int, C.c_int, C.POINTER(FSCamera), C.c_double,
                                       C.c_double, C.c_int, C.c_int, ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr,
                                       C.c_size_t, ptr]),
+    "fs_orb_search_for_initialization": (C.c_int, [ptr, ptr, ptr, ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, ptr,
+                                                   C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float,
+                                                   C.c_float, ptr, ptr, ptr]),
+    "fs_orb_stereo_matches": (C.c_int, [ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr, C.c_int, C.c_int, ptr, ptr, C.c_int,
+                                        C.c_int, C.c_float, C.c_float, ptr, ptr, ptr, ptr]),
+    "fs_render_forest": (C.c_int, [ptr, C.POINTER(FSCamera), C.c_double, C.c_double, ptr, C.c_int, C.c_int, C.c_int,
+                                   ptr, ptr, ptr]),
     "fs_rodrigues": (C.c_int, [ptr, C.c_int, ptr, ptr]),
     "fs_compose_trajectory": (C.c_int, [ptr, ptr, ptr, C.c_int, ptr, ptr, ptr]),
     "fs_transform_points": (C.c_int, [ptr, ptr, C.c_int, C.c_int, ptr, ptr, ptr]),

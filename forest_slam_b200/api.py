@@ -869,3 +869,83 @@ def solve_pnp_ransac(P3, p2, K, dist, *, reprojection_error: float = 1.0, confid
     """stereo_slam.py:294-295 → (ok, rvec, tvec, inliers)."""
     return solvePnPRansac(P3, p2, K, dist, reprojectionError=reprojection_error, confidence=confidence,
                           iterationsCount=iterations_count, flags=SOLVEPNP_ITERATIVE)
+
+
+# ------------------------------------------------------------------------------------------- §8f: guided ORB matching
+def orb_search_for_initialization(kpts, octave, desc, counts, pair_a, pair_b, prev_matched, *, angle=None,
+                                  window_size: int = 100, nn_ratio: float = 0.9, check_orientation: bool = True,
+                                  bounds=(0.0, 960.0, 0.0, 600.0)):
+    """ORBmatcher(nn_ratio, check_orientation).SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+    (ORB_SLAM3/src/ORBmatcher.cc:648-762; Tracking.cc:2491-2492 uses 0.9, true, 100) for a batch of frame pairs.
+    prev_matched [P, n_max, 2] is updated in place.  → dict(matches12 [P, n_max], n_matches [P], prev_matched)."""
+    lib = _lib.load()
+    kpts = _chk(kpts, torch.float32, "kpts")
+    dev = kpts.device
+    F, n_max = int(kpts.shape[0]), int(kpts.shape[1])
+    octave = _chk(octave, torch.int32, "octave")
+    desc = _chk(desc, torch.uint8, "desc")
+    counts = _chk(counts.to(dev), torch.int32, "counts")
+    if angle is not None:
+        angle = _chk(angle, torch.float32, "angle")
+    a, b = _pairs(pair_a, pair_b, dev)
+    P = int(a.numel())
+    prev_matched = _chk(prev_matched, torch.float32, "prev_matched")
+    if tuple(prev_matched.shape) != (P, n_max, 2):
+        raise ValueError("prev_matched must be [n_pairs, n_max, 2]")
+    m12 = torch.empty((P, n_max), dtype=torch.int32, device=dev)
+    nm = torch.empty((P,), dtype=torch.int32, device=dev)
+    _lib.check(lib.fs_orb_search_for_initialization(_p(kpts), _p(angle), _p(octave), _p(desc), F, n_max, _p(counts),
+                                                    _p(a), _p(b), P, _p(prev_matched), int(window_size),
+                                                    float(nn_ratio), int(bool(check_orientation)), float(bounds[0]),
+                                                    float(bounds[1]), float(bounds[2]), float(bounds[3]), _p(m12),
+                                                    _p(nm), _stream()), "fs_orb_search_for_initialization")
+    return {"matches12": m12, "n_matches": nm, "prev_matched": prev_matched}
+
+
+def orb_stereo_matches(kpts_l, octave_l, desc_l, counts_l, kpts_r, octave_r, desc_r, counts_r, image_l, image_r, *,
+                       camera: ForestCamera = ForestCamera(), baseline: Optional[float] = None):
+    """Frame::ComputeStereoMatches (ORB_SLAM3/src/Frame.cc:811-981) for a batch of stereo frames: row-band Hamming search,
+    SAD sub-pixel refinement on the image pair, median test.  → dict(u_right, depth, sad, disparity); `disparity`
+    (uL - uR, 0 where unmatched) is what the A6 back-projection of the stereo path reads per keypoint."""
+    lib = _lib.load()
+    kpts_l = _chk(kpts_l, torch.float32, "kpts_l")
+    kpts_r = _chk(kpts_r, torch.float32, "kpts_r")
+    dev = kpts_l.device
+    F, n_max = int(kpts_l.shape[0]), int(kpts_l.shape[1])
+    if tuple(kpts_r.shape) != tuple(kpts_l.shape):
+        raise ValueError("left and right keypoint banks must have the same [F, n_max, 2] shape")
+    image_l = _chk(image_l, torch.uint8, "image_l")
+    image_r = _chk(image_r, torch.uint8, "image_r")
+    rows, cols = int(image_l.shape[1]), int(image_l.shape[2])
+    B = camera.baseline if baseline is None else float(baseline)
+    ur = torch.empty((F, n_max), dtype=torch.float32, device=dev)
+    dp = torch.empty_like(ur)
+    sad = torch.empty((F, n_max), dtype=torch.int32, device=dev)
+    _lib.check(lib.fs_orb_stereo_matches(_p(kpts_l), _p(_chk(octave_l, torch.int32, "octave_l")),
+                                         _p(_chk(desc_l, torch.uint8, "desc_l")),
+                                         _p(_chk(counts_l.to(dev), torch.int32, "counts_l")), _p(kpts_r),
+                                         _p(_chk(octave_r, torch.int32, "octave_r")),
+                                         _p(_chk(desc_r, torch.uint8, "desc_r")),
+                                         _p(_chk(counts_r.to(dev), torch.int32, "counts_r")), F, n_max, _p(image_l),
+                                         _p(image_r), rows, cols, float(B), float(camera.fx * B), _p(ur), _p(dp),
+                                         _p(sad), _stream()), "fs_orb_stereo_matches")
+    disp = torch.where(ur >= 0, kpts_l[..., 0] - ur, torch.zeros_like(ur))
+    return {"u_right": ur, "depth": dp, "sad": sad, "disparity": disp}
+
+
+def render_forest(T_wc, trunks: torch.Tensor, *, camera: ForestCamera = ForestCamera(), baseline: Optional[float] = None,
+                  ground_y: float = 1.2, width: int = 960, height: int = 600, want_disparity: bool = True):
+    """CUDA ray caster (csrc/render.cu): grey image [H, W] u8 of the procedural forest (ground plane + trunk cylinders,
+    solid hashed texture) from camera pose T_wc, and the true dense disparity map [H, W] f32."""
+    lib = _lib.load()
+    trunks = _chk(trunks, torch.float64, "trunks")
+    dev = trunks.device
+    T = np.ascontiguousarray(T_wc, dtype=np.float64)
+    img = torch.empty((height, width), dtype=torch.uint8, device=dev)
+    disp = torch.empty((height, width), dtype=torch.float32, device=dev) if want_disparity else None
+    cam = camera.as_struct()
+    B = camera.baseline if baseline is None else float(baseline)
+    _lib.check(lib.fs_render_forest(T.ctypes.data_as(C.c_void_p), C.byref(cam), B, float(ground_y), _p(trunks),
+                                    int(trunks.shape[0]), int(width), int(height), _p(img), _p(disp), _stream()),
+               "fs_render_forest")
+    return img, disp

@@ -34,6 +34,8 @@ class ForestWorld:
     desc_bin: np.ndarray    # [L, 32] uint8
     desc_f32: np.ndarray    # [L, 256] float32 unit rows
     priority: np.ndarray    # [L] fixed random priority (keeps the keypoint set stable between frames)
+    trunks: Optional[np.ndarray] = None   # [n_trunks, 4] float64: axis x, axis z, radius, height (csrc/render.cu)
+    ground_y: float = 1.2                 # world y of the ground plane (y points down; the rig is at y = 0)
 
 
 def make_world(seed: int = SEED0, n_trunks: int = 400, pts_per_trunk: int = 60, n_ground: int = 8000,
@@ -64,7 +66,9 @@ def make_world(seed: int = SEED0, n_trunks: int = 400, pts_per_trunk: int = 60, 
     dbin = rng.integers(0, 256, (L, 32), dtype=np.uint8)
     df = rng.standard_normal((L, 256)).astype(np.float32)
     df /= np.linalg.norm(df, axis=1, keepdims=True)
-    return ForestWorld(points=pts, desc_bin=dbin, desc_f32=df, priority=rng.random(L))
+    return ForestWorld(points=pts, desc_bin=dbin, desc_f32=df, priority=rng.random(L),
+                       trunks=np.ascontiguousarray(np.stack([pos[:, 0], pos[:, 1], radius, height], axis=1)),
+                       ground_y=float(cam_height))
 
 
 def _rot_y(a):
@@ -181,6 +185,23 @@ def make_loop_sequence(n_frames: int, n_kpts: int, seed: int = SEED0, world: Opt
     world = world or make_world(seed)
     poses = make_loop_trajectory(n_frames, seed)
     return [observe(world, poses[i], n_kpts, seed + 50000 + i, **kw) for i in range(n_frames)]
+
+
+def right_pose(T_wc: np.ndarray, baseline: float = ForestCamera().baseline) -> np.ndarray:
+    """Pose of the right camera of the rectified rig: the left camera shifted by the baseline along its own +x."""
+    T = np.array(T_wc, dtype=np.float64)
+    T[:3, 3] = T[:3, 3] + T[:3, :3] @ np.array([baseline, 0.0, 0.0])
+    return T
+
+
+def keypoint_angles(world_size: int, landmark: np.ndarray, frame_seed: int, sigma: float = 2.0) -> np.ndarray:
+    """ORB-style keypoint orientation in degrees [0, 360): a fixed angle per landmark plus observation noise; spurious
+    keypoints get a random one (the synthetic frames have no image patch to take an orientation from)."""
+    base = np.random.default_rng(4242).uniform(0, 360, world_size)
+    rng = np.random.default_rng(frame_seed + 99)
+    a = np.where(landmark >= 0, base[np.maximum(landmark, 0)] + rng.normal(0, sigma, landmark.shape[0]),
+                 rng.uniform(0, 360, landmark.shape[0]))
+    return np.mod(a, 360.0).astype(np.float32)
 
 
 def relative_pose(f0: Frame, f1: Frame):

@@ -354,6 +354,50 @@ int fs_compose_trajectory(const double* R, const double* t, const int32_t* statu
 int fs_transform_points(const float* points3d, const int32_t* n_pts, int n_pairs, int n_max,
                         const double* T, float* out, fs_stream_t stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * SURVEY 8f rank 4 (second half): guided / windowed ORB matching — replaces
+ *       ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize)
+ *     ros_ws/src/ORB_SLAM3/src/ORBmatcher.cc:648-762 (call site src/Tracking.cc:2491-2492: ORBmatcher(0.9, true),
+ *     window 100), with Frame::GetFeaturesInArea / PosInGrid / AssignFeaturesToGrid (src/Frame.cc:657-735, :385-416:
+ *     64 x 48 grid, candidates in (ix, iy, insertion) order), ORBmatcher::DescriptorDistance (:2058-2074),
+ *     TH_LOW = 50, the ratio test, the sequential one-to-one stealing rule (:706-718) and the rotation histogram with
+ *     ComputeThreeMaxima (:719-755, :2012-2053), all exactly as the reference executes them.
+ * Frame bank: kpts [n_frames, n_max, 2] f32 (undistorted), angle [n_frames, n_max] f32 degrees (may be NULL when
+ * check_orientation == 0), octave [n_frames, n_max] i32, desc [n_frames, n_max, 32] u8, counts [n_frames].
+ * prev_matched [n_pairs, n_max, 2] f32 in/out (vbPrevMatched: search centres in, matched positions out),
+ * matches12 [n_pairs, n_max] i32 (-1 = none), n_matches [n_pairs].  Image bounds = mnMinX .. mnMaxY (Frame.cc:151-160).
+ * n_max <= 4096 (FS_ERR_UNSUPPORTED above). */
+int fs_orb_search_for_initialization(const float* kpts, const float* angle, const int32_t* octave,
+                                     const uint8_t* desc, int n_frames, int n_max, const int32_t* counts,
+                                     const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                                     float* prev_matched, int window_size, float nn_ratio, int check_orientation,
+                                     float min_x, float max_x, float min_y, float max_y,
+                                     int32_t* matches12, int32_t* n_matches, fs_stream_t stream);
+
+/* SURVEY 8f rank 1 (sparse variant) + rank 4 (row band): stereo correspondence feeding A6 — replaces
+ *       Frame::ComputeStereoMatches()      ros_ws/src/ORB_SLAM3/src/Frame.cc:811-981
+ *     row-band candidate table (:825-836), Hamming best below TH_HIGH in the disparity range (:858-897), 11 x 11 SAD
+ *     sliding window +-5 with parabola sub-pixel fit (:899-945), depth = mbf / disparity (:947-960), median test on the
+ *     correlation distance (:964-980).  Pyramid level 0 only (scale factor 1; the octave gates are kept).
+ * Left / right: kpts [n_frames, n_max, 2] f32, octave [n_frames, n_max] i32, desc [n_frames, n_max, 32] u8,
+ * counts [n_frames]; images [n_frames, rows, cols] u8.  mb = baseline (m), mbf = fx * baseline.
+ * Out: u_right, depth [n_frames, n_max] f32 (-1 = no match), sad [n_frames, n_max] i32 (correlation distance, -1 = none).
+ * A patch that would leave the image (the reference's cv::Mat::rowRange throws there) gives "no match". */
+int fs_orb_stereo_matches(const float* kpts_l, const int32_t* octave_l, const uint8_t* desc_l,
+                          const int32_t* counts_l, const float* kpts_r, const int32_t* octave_r,
+                          const uint8_t* desc_r, const int32_t* counts_r, int n_frames, int n_max,
+                          const uint8_t* image_l, const uint8_t* image_r, int rows, int cols, float mb, float mbf,
+                          float* u_right, float* depth, int32_t* sad, fs_stream_t stream);
+
+/* CUDA ray caster for the procedural forest (synthetic image pairs rasterised in CUDA; the reference
+ * reads its images from a rosbag, stereo_slam.py:35, :185-205).  T_wc_host: 4x4 row-major camera-to-world (host),
+ * trunks [n_trunks, 4] f64 on the device (x, z, radius, height), ground plane y = ground_y (y points down).
+ * image [height, width] u8; disparity [height, width] f32 = fx * baseline / Z_cam of the hit (0 for sky), may be NULL:
+ * a dense map for the lookup of stereo_slam.py:274-281. */
+int fs_render_forest(const double* T_wc_host, const FSCamera* cam_host, double baseline, double ground_y,
+                     const double* trunks, int n_trunks, int width, int height, uint8_t* image, float* disparity,
+                     fs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

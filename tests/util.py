@@ -120,3 +120,67 @@ def host_harness():
 
 def vp(a):
     return a.ctypes.data_as(C.c_void_p)
+
+
+_orb = None
+
+
+def orb_oracle():
+    """TEST-ONLY: oracle/orb_guided.c (the reference's ORB-SLAM3 guided matchers restated in C) as a ctypes library."""
+    global _orb
+    if _orb is None:
+        import __graft_entry__ as ge
+        ge._build_oracle()
+        _orb = C.CDLL(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_build",
+                                   "liboracle.so"))
+        _orb.orb_search_for_initialization.restype = C.c_int
+        _orb.orb_search_for_initialization.argtypes = [C.c_int] + [C.c_void_p] * 4 + [C.c_int] + [C.c_void_p] * 4 + [
+            C.c_void_p, C.c_int, C.c_float, C.c_int, C.c_float, C.c_float, C.c_float, C.c_float, C.c_void_p]
+        _orb.orb_compute_stereo_matches.restype = None
+        _orb.orb_compute_stereo_matches.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                                    C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p]
+        _orb.orb_descriptor_distance.restype = C.c_int
+        _orb.orb_descriptor_distance.argtypes = [C.c_void_p, C.c_void_p]
+    return _orb
+
+
+def orb_search_init_oracle(kp1, ang1, oct1, d1, kp2, ang2, oct2, d2, prev, window=100, ratio=0.9, check=True,
+                           bounds=(0.0, 960.0, 0.0, 600.0)):
+    """-> (matches12 [n1] int32, n_matches, prev_matched updated copy)"""
+    lib = orb_oracle()
+    c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+    kp1, kp2, prev = c(kp1, np.float32), c(kp2, np.float32), c(prev, np.float32).copy()
+    ang1, ang2 = c(ang1, np.float32), c(ang2, np.float32)
+    oct1, oct2, d1, d2 = c(oct1, np.int32), c(oct2, np.int32), c(d1, np.uint8), c(d2, np.uint8)
+    m12 = np.empty(kp1.shape[0], np.int32)
+    n = lib.orb_search_for_initialization(kp1.shape[0], vp(kp1), vp(ang1), vp(oct1), vp(d1), kp2.shape[0], vp(kp2),
+                                          vp(ang2), vp(oct2), vp(d2), vp(prev), int(window), float(ratio), int(check),
+                                          bounds[0], bounds[1], bounds[2], bounds[3], vp(m12))
+    return m12, n, prev
+
+
+def orb_stereo_oracle(kpL, octL, dL, kpR, octR, dR, imL, imR, mb, mbf):
+    """-> (u_right, depth, sad)"""
+    lib = orb_oracle()
+    c = lambda a, dt: np.ascontiguousarray(a, dtype=dt)
+    kpL, kpR = c(kpL, np.float32), c(kpR, np.float32)
+    octL, octR, dL, dR = c(octL, np.int32), c(octR, np.int32), c(dL, np.uint8), c(dR, np.uint8)
+    imL, imR = c(imL, np.uint8), c(imR, np.uint8)
+    n = kpL.shape[0]
+    ur, dp, sad = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.int32)
+    lib.orb_compute_stereo_matches(n, vp(kpL), vp(octL), vp(dL), kpR.shape[0], vp(kpR), vp(octR), vp(dR), vp(imL),
+                                   vp(imR), imL.shape[0], imL.shape[1], float(mb), float(mbf), vp(ur), vp(dp), vp(sad))
+    return ur, dp, sad
+
+
+def stereo_scene(n_kpts=1200, seed=0, n_trunks=60, border=16, pose_index=3):
+    """A rendered stereo frame for the ORB stereo tests: world with trunk geometry, left/right keypoints + descriptors
+    observed from the rectified rig, and the two poses.  (Images come from the renderer under test.)"""
+    from forest_slam_b200 import synth
+    world = synth.make_world(synth.SEED0 + seed, n_trunks=n_trunks, n_ground=6000, n_canopy=500)
+    T_l = synth.make_trajectory(pose_index + 1, synth.SEED0 + seed)[pose_index]
+    T_r = synth.right_pose(T_l)
+    fl = synth.observe(world, T_l, n_kpts, 7000 + seed, border=border)
+    fr = synth.observe(world, T_r, n_kpts, 8000 + seed, border=border)
+    return world, T_l, T_r, fl, fr
