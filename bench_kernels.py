@@ -271,6 +271,68 @@ def main():
         line("k_gather_matches", {"pairs": P, "n": n}, ms, {"bytes": byts}, "hbm", byts / ms / 1e6, pk["hbm_gbs"],
              "GB/s", "latency-bound at this size (a few MB per launch)")
 
+    # ------------------------------------------------------------------ guided ORB matching + ray caster (§8f ranks 1, 4)
+    if on("orb"):
+        from tests import util as tu
+        cam = fsb.ForestCamera()
+        world = synth.make_world(synth.SEED0)
+        # SearchForInitialization: 256 temporal pairs of 2000 keypoints, window 100
+        Pn, n = min(P, 256), 2000
+        frames = synth.make_sequence(Pn + 1, n, world=world)
+        kp = torch.from_numpy(np.stack([f.kpts for f in frames])).to(dev)
+        desc = torch.from_numpy(np.stack([f.desc_bin for f in frames])).to(dev)
+        ang = torch.from_numpy(np.stack([synth.keypoint_angles(world.points.shape[0], f.landmark, i)
+                                         for i, f in enumerate(frames)])).to(dev)
+        octv = torch.zeros((Pn + 1, n), dtype=torch.int32, device=dev)
+        counts = torch.full((Pn + 1,), n, dtype=torch.int32, device=dev)
+        a = torch.arange(Pn, dtype=torch.int32, device=dev)
+        b = a + 1
+        prev0 = kp[:Pn].clone()
+        r = fsb.orb_search_for_initialization(kp, octv, desc, counts, a, b, prev0.clone(), angle=ang)
+        ms = T(lambda: fsb.orb_search_for_initialization(kp, octv, desc, counts, a, b, prev0.clone(), angle=ang))
+        cand = Pn * n * (200.0 * 200.0) / (960.0 * 600.0) * n
+        line("k_orb_search_init (ORBmatcher::SearchForInitialization, window 100)", {"pairs": Pn, "kpts": n}, ms,
+             {"candidate_distances": cand, "popc32": cand * 8, "pairs_per_s": Pn / ms * 1e3,
+              "mean_matches": float(r["n_matches"].float().mean())}, "latency (sequential greedy loop per pair)",
+             cand * 8 / ms / 1e6, pp["popc_gops"], "Gpopc32/s",
+             "one warp per frame pair walks the queries IN ORDER (later queries depend on earlier assignments); "
+             "the batch supplies the parallelism")
+        # ray caster: stereo pair at 960 x 600, 400 trunks
+        tr = torch.from_numpy(world.trunks).to(dev)
+        T_l = frames[3].T_wc
+        ms = T(lambda: fsb.render_forest(T_l, tr, ground_y=world.ground_y))
+        px = 960 * 600.0
+        line("k_render_forest (ray caster, 400 trunk cylinders + ground plane)", {"image": "960x600"}, ms,
+             {"ray_cylinder_tests": px * 400, "flop": px * 400 * 14, "bytes_out": px * 5}, "fp64 pipe",
+             px * 400 * 14 / ms / 1e9, pp["fp64_tflops_no_fma"], "TFLOP/s",
+             "one thread per pixel, every trunk tested (fp64, no FMA: bit-identical to the NumPy restatement)")
+        # ComputeStereoMatches on 16 rendered stereo frames
+        Fn = 16
+        imL = torch.empty((Fn, 600, 960), dtype=torch.uint8, device=dev)
+        imR = torch.empty_like(imL)
+        kL, kR, dL, dR = [], [], [], []
+        for f in range(Fn):
+            T_l = frames[2 + f].T_wc
+            T_r = synth.right_pose(T_l)
+            imL[f] = fsb.render_forest(T_l, tr, ground_y=world.ground_y, want_disparity=False)[0]
+            imR[f] = fsb.render_forest(T_r, tr, ground_y=world.ground_y, want_disparity=False)[0]
+            fl = synth.observe(world, T_l, n, 500 + f, border=16)
+            fr = synth.observe(world, T_r, n, 900 + f, border=16)
+            kL.append(fl.kpts); kR.append(fr.kpts); dL.append(fl.desc_bin); dR.append(fr.desc_bin)
+        tt = lambda x, dt: torch.from_numpy(np.stack(x)).to(dev).to(dt)
+        kL, kR, dL, dR = tt(kL, torch.float32), tt(kR, torch.float32), tt(dL, torch.uint8), tt(dR, torch.uint8)
+        oz = torch.zeros((Fn, n), dtype=torch.int32, device=dev)
+        cn = torch.full((Fn,), n, dtype=torch.int32, device=dev)
+        r = fsb.orb_stereo_matches(kL, oz, dL, cn, kR, oz, dR, cn, imL, imR)
+        ms = T(lambda: fsb.orb_stereo_matches(kL, oz, dL, cn, kR, oz, dR, cn, imL, imR))
+        nm = float((r["u_right"] >= 0).float().sum(1).mean())
+        byts = Fn * (2 * n * (8 + 32 + 4) + n * 12.0)
+        line("k_orb_stereo + k_orb_stereo_median (Frame::ComputeStereoMatches)", {"frames": Fn, "kpts": n}, ms,
+             {"row_band_tests": Fn * n * n * 1.0, "bytes": byts, "frames_per_s": Fn / ms * 1e3, "mean_matched": nm},
+             "hbm", byts / ms / 1e6, pk["hbm_gbs"], "GB/s",
+             "one warp per left keypoint: row-band scan of the right keypoints, 11 x 11 SAD x 11 shifts, parabola fit; "
+             "latency-bound at this size")
+
     # ------------------------------------------------------------------ SuperGlue score head (Sinkhorn, §8f rank 2)
     if on("sinkhorn"):
         for (m, n, pp) in ((1024, 1024, 64), (2048, 2048, 16)):
