@@ -119,7 +119,7 @@ def main():
     dev = torch.device("cuda:0")
     torch.cuda.set_device(dev)
     pk = peaks()
-    pp = pipe_peaks()
+    pipes = pipe_peaks()
     ghz = sm_clock_ghz()
     T = Timer(args.reps)
     P = args.pairs
@@ -129,7 +129,7 @@ def main():
     def on(name):
         return want is None or name in want
 
-    print(json.dumps({"peaks": pk, "pipe_peaks": pp, "sm_clock_ghz": ghz, "sms": SMS,
+    print(json.dumps({"peaks": pk, "pipe_peaks": pipes, "sm_clock_ghz": ghz, "sms": SMS,
                       "device": torch.cuda.get_device_name(0)}))
 
     # ------------------------------------------------------------------ A2 Hamming (POPC pipe; HBM figure asked too)
@@ -143,7 +143,7 @@ def main():
             ms = T(lambda: fsb.hamming_match_batch(desc, counts, a, b, popc=True))
             popc = P * n * n * 8.0
             byts = P * ((n + n) * 32 + n * 12.0)
-            peak_popc = pp["popc_gops"]  # measured G popc32/s (16 lanes/clk/SM)
+            peak_popc = pipes["popc_gops"]  # measured G popc32/s (16 lanes/clk/SM)
             line("k_hamming_top2 (+finalize)", {"pairs": P, "n0": n, "n1": n, "crossCheck": True}, ms,
                  {"popc32": popc, "bytes": byts, "hbm_gbs": byts / ms / 1e6}, "popc pipe",
                  popc / ms / 1e6, peak_popc, "Gpopc32/s",
@@ -236,7 +236,7 @@ def main():
         P3 = rng.uniform([-10, -3, 2], [10, 3, 40], (Pn, K, 3)).astype(np.float32)
         nc = torch.full((Pn,), K, dtype=torch.int32, device=dev)
         x0t, x1t, P3t = (torch.from_numpy(v).to(dev) for v in (x0, x1, P3))
-        fp64_peak = pp["fp64_tflops_no_fma"]  # measured DMUL + DADD rate (the scorers run without FMA contraction)
+        fp64_peak = pipes["fp64_tflops_no_fma"]  # measured DMUL + DADD rate (the scorers run without FMA contraction)
         for H in (1024, 2048, 4096, 8192, 16384, 32768, 65536):
             E = torch.from_numpy(rng.normal(0, 1, (Pn, H, 3, 3))).to(dev)
             ms = T(lambda: fsb.score_essential_batch(x0t, x1t, nc, E, focal=cam.fx, pp=(cam.cx, cam.cy)))
@@ -294,7 +294,7 @@ def main():
         line("k_orb_search_init (ORBmatcher::SearchForInitialization, window 100)", {"pairs": Pn, "kpts": n}, ms,
              {"candidate_distances": cand, "popc32": cand * 8, "pairs_per_s": Pn / ms * 1e3,
               "mean_matches": float(r["n_matches"].float().mean())}, "latency (sequential greedy loop per pair)",
-             cand * 8 / ms / 1e6, pp["popc_gops"], "Gpopc32/s",
+             cand * 8 / ms / 1e6, pipes["popc_gops"], "Gpopc32/s",
              "one warp per frame pair walks the queries IN ORDER (later queries depend on earlier assignments); "
              "the batch supplies the parallelism")
         # ray caster: stereo pair at 960 x 600, 400 trunks
@@ -304,7 +304,7 @@ def main():
         px = 960 * 600.0
         line("k_render_forest (ray caster, 400 trunk cylinders + ground plane)", {"image": "960x600"}, ms,
              {"ray_cylinder_tests": px * 400, "flop": px * 400 * 14, "bytes_out": px * 5}, "fp64 pipe",
-             px * 400 * 14 / ms / 1e9, pp["fp64_tflops_no_fma"], "TFLOP/s",
+             px * 400 * 14 / ms / 1e9, pipes["fp64_tflops_no_fma"], "TFLOP/s",
              "one thread per pixel, every trunk tested (fp64, no FMA: bit-identical to the NumPy restatement)")
         # ComputeStereoMatches on 16 rendered stereo frames
         Fn = 16
@@ -343,7 +343,7 @@ def main():
             ms = T(lambda: fsb.sinkhorn_match_batch(sc, cm, cn, iters=iters))
             ex2 = pp * m * n * 2.0 * iters
             byts = pp * m * n * 4.0
-            peak_mufu = pp["ex2_gops"]  # measured G ex2/s (16 MUFU lanes/clk/SM)
+            peak_mufu = pipes["ex2_gops"]  # measured G ex2/s (16 MUFU lanes/clk/SM)
             line("k_sk_resident (cooperative, 1 launch per group)", {"pairs": pp, "m": m, "n": n, "iters": iters}, ms,
                  {"ex2": ex2, "bytes_hbm_once": byts, "bytes_streamed": byts * (iters + 1),
                   "stream_gbs": byts * (iters + 1) / ms / 1e6, "pairs_per_s": pp / ms * 1e3}, "mufu pipe",
