@@ -63,8 +63,9 @@ k_orb_search_init(OrbInitParams P) {
     unsigned short* s_idx = reinterpret_cast<unsigned short*>(orb_smem + (size_t)NM * 40);   // mGrid cell lists (CSR)
     unsigned short* s_mdist = s_idx + NM;                                                // vMatchedDistance (0xFFFF = INT_MAX)
     short* s_m21 = reinterpret_cast<short*>(s_mdist + NM);                               // vnMatches21
-    signed char* s_bin = reinterpret_cast<signed char*>(s_m21 + NM);                     // rotHist bin of query i1
-    unsigned char* s_oct2 = reinterpret_cast<unsigned char*>(s_bin + NM);                // octave of frame 2 (clamped to 255)
+    unsigned short* s_push = reinterpret_cast<unsigned short*>(s_m21 + NM);              // partner of query i1 when it was
+    //                                                        pushed into rotHist (0xFFFF: never); the bin is computed after the loop
+    unsigned char* s_oct2 = reinterpret_cast<unsigned char*>(s_push + NM);               // octave of frame 2 (clamped to 255)
     const int p = blockIdx.x, lane = threadIdx.x;
     const unsigned full = 0xffffffffu;
     const int fa = P.pair_a[p], fb = P.pair_b[p];
@@ -92,7 +93,7 @@ k_orb_search_init(OrbInitParams P) {
     for (int i = lane; i < P.n_max; i += 32) {
         s_mdist[i] = 0xFFFF;
         s_m21[i] = -1;
-        s_bin[i] = -1;
+        s_push[i] = 0xFFFF;
         if (i < n1) m12[i] = -1;
     }
     __syncwarp();
@@ -130,12 +131,31 @@ k_orb_search_init(OrbInitParams P) {
         __syncwarp();
     }
 
-    // ---- the sequential loop of ORBmatcher.cc:663-729
+    // ---- the sequential loop of ORBmatcher.cc:663-729.  The next query's inputs (search centre, octave, descriptor) are
+    // fetched from global memory one iteration ahead; the rotation histogram is filled after the loop (its counts do not
+    // depend on the order of the pushes), so that no global round trip sits on the loop's dependency chain.
     const float r = (float)P.window;
     const float factor = 1.0f / HISTO_LENGTH;  // :656, the reference's factor
+    float2 nq = make_float2(0.f, 0.f);
+    int noct = 1;
+    uint4 na0 = make_uint4(0, 0, 0, 0), na1 = na0;
+    if (n1 > 0) {
+        nq = prev[0];
+        noct = oct1[0];
+        na0 = d1[0];
+        na1 = d1[1];
+    }
     for (int i1 = 0; i1 < n1; i1++) {
-        if (oct1[i1] > 0) continue;  // level1 > 0 (:666)
-        const float2 q = prev[i1];   // vbPrevMatched[i1]
+        const float2 q = nq;   // vbPrevMatched[i1]
+        const int level1 = noct;
+        const uint4 a0 = na0, a1 = na1;
+        if (i1 + 1 < n1) {
+            nq = prev[i1 + 1];
+            noct = oct1[i1 + 1];
+            na0 = d1[2 * i1 + 2];
+            na1 = d1[2 * i1 + 3];
+        }
+        if (level1 > 0) continue;  // :666
         // Frame::GetFeaturesInArea(x, y, windowSize, 0, 0)   Frame.cc:657-723
         int cx0 = (int)floorf((q.x - P.minx - r) * P.winv);
         cx0 = max(cx0, 0);
@@ -146,31 +166,59 @@ k_orb_search_init(OrbInitParams P) {
         if (cy0 >= GRID_ROWS) continue;
         int cy1 = min(GRID_ROWS - 1, (int)ceilf((q.y - P.miny + r) * P.hinv));
         if (cy1 < 0) continue;
-        const int ncy = cy1 - cy0 + 1, ncells = (cx1 - cx0 + 1) * ncy;
-        const uint4 a0 = d1[2 * i1], a1 = d1[2 * i1 + 1];
-        // key = dist << 20 | visiting order of the cell << 8 | position in the cell: unique, so the two smallest keys are
-        // (bestDist with the FIRST index reaching it, bestDist2) of the reference's strict-less scan
+        // The cells (ix, cy0 .. cy1) of one grid column are consecutive in the CSR (cell = ix * ROWS + iy), so a column of the
+        // window is ONE contiguous candidate range, visited in the reference's (iy, insertion) order.  One column per
+        // lane; the columns' candidates are then dealt evenly over the lanes (a cell on a trunk or on the horizon holds
+        // dozens of keypoints, most none).  key = dist << 20 | column << 12 | position in the column's range: unique,
+        // so the two smallest keys are (bestDist with the FIRST index reaching it, bestDist2) of the strict-less scan.
+        const int ncx = cx1 - cx0 + 1;
         unsigned k1 = 0xFFFFFFFFu, k2 = 0xFFFFFFFFu;
         int idx = -1;
-        for (int c0 = 0; c0 < ncells; c0 += 32) {
+        for (int c0 = 0; c0 < ncx; c0 += 32) {
             const int k = c0 + lane;
-            if (k < ncells) {
-                const int cell = (cx0 + k / ncy) * GRID_ROWS + cy0 + k % ncy;
-                const int s = s_start[cell], e = s_start[cell + 1];
-                for (int j = s; j < e; j++) {
-                    const int i2 = s_idx[j];
-                    if (s_oct2[i2] != 0) continue;  // kpUn.octave < minLevel or > maxLevel, minLevel = maxLevel = 0
-                    const float2 t = kp2[i2];
-                    if (!(fabsf(t.x - q.x) < r && fabsf(t.y - q.y) < r)) continue;
-                    const int dist = desc_distance(a0, a1, d2 + 2 * i2);
-                    if ((int)s_mdist[i2] <= dist) continue;  // vMatchedDistance[i2] <= dist (0xFFFF plays INT_MAX)
-                    const unsigned key = ((unsigned)dist << 20) | ((unsigned)k << 8) | (unsigned)min(j - s, 255);
-                    if (key < k1) {
-                        k2 = k1;
-                        k1 = key;
-                        idx = i2;
-                    } else if (key < k2) {
-                        k2 = key;
+            int cs = 0, cn = 0;
+            if (k < ncx) {
+                const int cell0 = (cx0 + k) * GRID_ROWS + cy0;
+                cs = s_start[cell0];
+                cn = s_start[cell0 + (cy1 - cy0) + 1] - cs;
+            }
+            int incl = cn;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(full, incl, o);
+                if (lane >= o) incl += v;
+            }
+            const int total = __shfl_sync(full, incl, 31);
+            for (int t0 = 0; t0 < total; t0 += 32) {
+                const int t = t0 + lane;
+                // owner = first lane whose inclusive count exceeds t (binary search over the warp's scan)
+                int lo = 0;
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) {
+                    const int v = __shfl_sync(full, incl, lo + step - 1);
+                    if (v <= t) lo += step;
+                }
+                const int owner = min(lo, 31);
+                const int o_incl = __shfl_sync(full, incl, owner), o_cn = __shfl_sync(full, cn, owner);
+                const int o_cs = __shfl_sync(full, cs, owner);
+                if (t < total) {
+                    const int pos = t - (o_incl - o_cn);
+                    const int i2 = s_idx[o_cs + pos];
+                    if (s_oct2[i2] == 0) {  // kpUn.octave < minLevel or > maxLevel, minLevel = maxLevel = 0
+                        const float2 tp = kp2[i2];
+                        if (fabsf(tp.x - q.x) < r && fabsf(tp.y - q.y) < r) {
+                            const int dist = desc_distance(a0, a1, d2 + 2 * i2);
+                            if (!((int)s_mdist[i2] <= dist)) {  // vMatchedDistance[i2] <= dist -> skip (0xFFFF plays INT_MAX)
+                                const unsigned key = ((unsigned)dist << 20) | ((unsigned)(c0 + owner) << 12) | (unsigned)pos;
+                                if (key < k1) {
+                                    k2 = k1;
+                                    k1 = key;
+                                    idx = i2;
+                                } else if (key < k2) {
+                                    k2 = key;
+                                }
+                            }
+                        }
                     }
                 }
             }
@@ -190,16 +238,7 @@ k_orb_search_init(OrbInitParams P) {
                 m12[i1] = bestIdx2;
                 s_m21[bestIdx2] = (short)i1;
                 s_mdist[bestIdx2] = (unsigned short)bestDist;
-                if (P.check_orientation) {
-                    const float* ang1 = P.angle + (size_t)fa * P.n_max;
-                    const float* ang2 = P.angle + (size_t)fb * P.n_max;
-                    float rot = ang1[i1] - ang2[bestIdx2];
-                    if (rot < 0.0f) rot += 360.0f;
-                    int bin = (int)roundf(rot * factor);
-                    if (bin == HISTO_LENGTH) bin = 0;
-                    s_hist[bin]++;
-                    s_bin[i1] = (signed char)bin;
-                }
+                s_push[i1] = (unsigned short)bestIdx2;   // rotHist[bin].push_back(i1), bin from this partner (:719-729)
             }
             __syncwarp();
         }
@@ -207,6 +246,19 @@ k_orb_search_init(OrbInitParams P) {
     __syncwarp();
     // ---- rotation consistency (:731-755) with ORBmatcher::ComputeThreeMaxima (:2012-2053)
     if (P.check_orientation) {
+        const float* ang1 = P.angle + (size_t)fa * P.n_max;
+        const float* ang2 = P.angle + (size_t)fb * P.n_max;
+        for (int i = lane; i < n1; i += 32) {
+            const int partner = s_push[i];
+            if (partner == 0xFFFF) continue;
+            float rot = ang1[i] - ang2[partner];
+            if (rot < 0.0f) rot += 360.0f;
+            int bin = (int)roundf(rot * factor);
+            if (bin == HISTO_LENGTH) bin = 0;
+            atomicAdd(&s_hist[bin], 1);
+            s_push[i] = (unsigned short)bin;   // from here on: the bin of query i
+        }
+        __syncwarp();
         int ind1 = -1, ind2 = -1, ind3 = -1;
         int max1 = 0, max2 = 0, max3 = 0;
         for (int i = 0; i < HISTO_LENGTH; i++) {
@@ -229,8 +281,8 @@ k_orb_search_init(OrbInitParams P) {
             ind3 = -1;
         }
         for (int i = lane; i < n1; i += 32) {
-            const int b = s_bin[i];
-            if (b >= 0 && b != ind1 && b != ind2 && b != ind3) m12[i] = -1;
+            const int b = s_push[i];
+            if (b != 0xFFFF && b != ind1 && b != ind2 && b != ind3) m12[i] = -1;
         }
         __syncwarp();
     }
@@ -457,8 +509,8 @@ extern "C" int fs_orb_search_for_initialization(const float* kpts, const float* 
     P.nn_ratio = nn_ratio; P.minx = min_x; P.miny = min_y;
     P.winv = (float)GRID_COLS / (max_x - min_x);   // Frame.cc:159-160
     P.hinv = (float)GRID_ROWS / (max_y - min_y);
-    // frame 2 staged in shared memory: 32 B descriptor + 8 B position + 2+2+2+1+1 B of state per keypoint
-    const size_t smem = (size_t)n_max * 48 + 64;
+    // frame 2 staged in shared memory: 32 B descriptor + 8 B position + 2+2+2+2+1 B of state per keypoint
+    const size_t smem = (size_t)n_max * 49 + 64;
     static int granted[64];
     const int st_ = fs::ensure_dyn_smem(k_orb_search_init, granted, smem);
     if (st_ != FS_OK) return st_;
