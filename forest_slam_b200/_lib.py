@@ -45,6 +45,8 @@ SIGNATURES = {
     "fs_float_match_split3_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "fs_float_match": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,
                                  C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
+    "fs_float_match_knn": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,
+                                     C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_top3_keys": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_int, ptr, ptr, C.c_size_t, ptr]),
     "fs_float_match_split3": (C.c_int, [ptr, C.c_int, C.c_int, ptr, ptr, ptr, C.c_int, C.c_float, C.c_float,
                                         C.c_float, ptr, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),

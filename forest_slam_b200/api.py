@@ -235,7 +235,7 @@ FLOAT_TOP3_MAX_COLS = 4096  # fs_float_match packs the column index into 12 key 
 def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, *, scale: float = 1.0,
                       threshold: Optional[float] = None, ratio: Optional[float] = None,
                       operands: Optional[torch.Tensor] = None, exact_fp32: bool = False, split3: bool = False,
-                      want_diag: bool = False):
+                      want_diag: bool = False, cross_check: bool = True):
     """Batched float-descriptor mutual-NN (+threshold, +ratio): superglue.py:259-260, :268-278.
 
     desc [F, 256, n_max] fp32.  Default: the certified single-pass tcgen05 kernel on the fp16 operand bank
@@ -264,6 +264,8 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
     use_tc = TENSOR_CORE_MATCHER and (not exact_fp32) and n_max % 128 == 0
     if use_tc and n_max > FLOAT_TOP3_MAX_COLS:
         split3 = True
+    if not cross_check and (not use_tc or split3):
+        raise ValueError("cross_check=False runs on the certified tensor-core kernel: n_max % 128 == 0, n_max <= 4096")
     out = {"matches0": m0, "matches1": m1, "score0": sc, "second0": se, "n_matches": nm}
     if use_tc:
         if operands is None:
@@ -279,6 +281,14 @@ def float_match_batch(desc: torch.Tensor, counts: torch.Tensor, pair_a, pair_b, 
         else:
             ws = _workspace(lib.fs_float_match_tc_workspace_bytes(P, n_max), dev)
             diag = torch.empty((4,), dtype=torch.int32, device=dev) if want_diag else None
+            if not cross_check:
+                _lib.check(lib.fs_float_match_knn(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
+                                                  rat, _p(m0), _p(sc), _p(se), _p(nm), _p(diag), _p(ws), ws.numel(),
+                                                  _stream()), "fs_float_match_knn")
+                out["matches1"] = None
+                if want_diag:
+                    out["diag"] = diag
+                return out
             _lib.check(lib.fs_float_match(_p(operands), F, n_max, _p(counts), _p(a), _p(b), P, float(scale), thr,
                                           rat, _p(m0), _p(sc), _p(se), _p(m1), _p(nm), _p(diag), _p(ws), ws.numel(),
                                           _stream()), "fs_float_match")
@@ -710,10 +720,8 @@ class BFMatcher:
         bank[0, :, :n0] = _to_cuda(d0, torch.float32, dev).T
         bank[1, :, :n1] = _to_cuda(d1, torch.float32, dev).T
         counts = torch.tensor([n0, n1], dtype=torch.int32, device=dev)
-        r = float_match_batch(bank, counts, [0], [1], ratio=ratio)
+        r = float_match_batch(bank, counts, [0], [1], ratio=ratio, cross_check=self.crossCheck)
         m0 = r["matches0"][0, :n0].cpu().numpy()
-        if not self.crossCheck:
-            raise NotImplementedError("NORM_L2 is exposed with crossCheck=True only (superglue.py:270 semantics)")
         cos = r["score0"][0, :n0].cpu().numpy()
         cos2 = r["second0"][0, :n0].cpu().numpy()
         d = np.sqrt(np.maximum(0.0, 2.0 - 2.0 * cos)).astype(np.float32)

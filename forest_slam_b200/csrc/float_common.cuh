@@ -50,6 +50,6 @@ struct FloatRowTop2 {
 int launch_float_finalize(int n_max, const int32_t* counts, const int32_t* pair_a, const int32_t* pair_b,
                           int n_pairs, FloatRowTop2 d0, const int32_t* idx1, float scale, float threshold,
                           float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
-                          int32_t* n_matches, cudaStream_t stream);
+                          int32_t* n_matches, cudaStream_t stream, int cross_check = 1);
 
 }  // namespace fs

@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(256)
 k_float_finalize(int n_max, const int32_t* __restrict__ counts, const int32_t* __restrict__ pair_a,
                  const int32_t* __restrict__ pair_b, const float* __restrict__ best0,
                  const float* __restrict__ sec0, const int32_t* __restrict__ idx0,
-                 const int32_t* __restrict__ idx1, float scale, float threshold, float ratio,
+                 const int32_t* __restrict__ idx1, float scale, float threshold, float ratio, int cross_check,
                  int32_t* __restrict__ matches0, float* __restrict__ score0, float* __restrict__ second0,
                  int32_t* __restrict__ matches1, int32_t* __restrict__ n_matches) {
     const int p = blockIdx.y;
@@ -111,7 +111,7 @@ k_float_finalize(int n_max, const int32_t* __restrict__ counts, const int32_t* _
             const int i0 = idx0[o];
             sb = __fmul_rn(b, scale);
             ss = __fmul_rn(s, scale);
-            ok = idx1[(size_t)p * n_max + i0] == n;      // mutual0, superglue.py:270
+            ok = !cross_check || idx1[(size_t)p * n_max + i0] == n;      // mutual0, superglue.py:270 (knn use: no check)
             ok = ok && (sb > threshold);                  // valid0, superglue.py:275
             if (ratio > 0.f) {
                 // Lowe ratio on the L2 distance of unit vectors, d = sqrt(max(0, 2 - 2 cos)); strict <
@@ -121,7 +121,7 @@ k_float_finalize(int n_max, const int32_t* __restrict__ counts, const int32_t* _
             }
             if (ok) {
                 m = i0;
-                if (matches1) matches1[(size_t)p * n_max + i0] = n;  // mutual => unique writer
+                if (matches1 && cross_check) matches1[(size_t)p * n_max + i0] = n;  // mutual => unique writer
             }
         }
         matches0[o] = m;
@@ -141,7 +141,7 @@ namespace fs {
 int launch_float_finalize(int n_max, const int32_t* counts, const int32_t* pair_a, const int32_t* pair_b,
                           int n_pairs, FloatRowTop2 d0, const int32_t* idx1, float scale, float threshold,
                           float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
-                          int32_t* n_matches, cudaStream_t stream) {
+                          int32_t* n_matches, cudaStream_t stream, int cross_check) {
     const size_t n = (size_t)n_pairs * n_max;
     if (matches1) FS_CUDA(cudaMemsetAsync(matches1, 0xFF, n * sizeof(int32_t), stream));
     if (n_matches) FS_CUDA(cudaMemsetAsync(n_matches, 0, (size_t)n_pairs * sizeof(int32_t), stream));
@@ -151,7 +151,7 @@ int launch_float_finalize(int n_max, const int32_t* counts, const int32_t* pair_
         dim3 g((n_max + 255) / 256, np);
         k_float_finalize<<<g, 256, 0, stream>>>(n_max, counts, pair_a + p0, pair_b + p0, d0.best + o,
                                                 d0.second + o, d0.idx + o, idx1 + o, scale, threshold, ratio,
-                                                matches0 + o, score0 ? score0 + o : nullptr,
+                                                cross_check, matches0 + o, score0 ? score0 + o : nullptr,
                                                 second0 ? second0 + o : nullptr,
                                                 matches1 ? matches1 + o : nullptr,
                                                 n_matches ? n_matches + p0 : nullptr);

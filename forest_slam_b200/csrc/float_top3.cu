@@ -496,11 +496,11 @@ extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max,
                        ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_, probe, trace);
 }
 
-extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, const int32_t* counts,
-                              const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float threshold,
-                              float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
-                              int32_t* n_matches, int32_t* diag, void* workspace, size_t workspace_bytes,
-                              fs_stream_t stream_) {
+static int float_match_impl(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                            const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float threshold,
+                            float ratio, int cross_check, int32_t* matches0, float* score0, float* second0,
+                            int32_t* matches1, int32_t* n_matches, int32_t* diag, void* workspace,
+                            size_t workspace_bytes, fs_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
     FS_REQUIRE(n_pairs >= 0 && n_frames >= 0 && n_max >= 0, "negative size");
     if (n_pairs == 0 || n_max == 0) return FS_OK;
@@ -545,5 +545,25 @@ extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, con
     if (diag) FS_CUDA(cudaMemcpyAsync(diag, out.counters, 4 * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     fs::FloatRowTop2 d0{out.best, out.second, out.idx};
     return fs::launch_float_finalize(n_max, counts, pair_a, pair_b, n_pairs, d0, out.idx + n, scale, threshold, ratio,
-                                     matches0, score0, second0, matches1, n_matches, stream);
+                                     matches0, score0, second0, matches1, n_matches, stream, cross_check);
+}
+
+extern "C" int fs_float_match(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                              const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale, float threshold,
+                              float ratio, int32_t* matches0, float* score0, float* second0, int32_t* matches1,
+                              int32_t* n_matches, int32_t* diag, void* workspace, size_t workspace_bytes,
+                              fs_stream_t stream_) {
+    return float_match_impl(operands, n_frames, n_max, counts, pair_a, pair_b, n_pairs, scale, threshold, ratio, 1,
+                            matches0, score0, second0, matches1, n_matches, diag, workspace, workspace_bytes, stream_);
+}
+
+// BFMatcher(NORM_L2).knnMatch(k = 2) + Lowe ratio WITHOUT the mutual check (ORB_SLAM3/src/Frame.cc:1144-1151 semantics for
+// float descriptors): matches0[q] = best column of row q if it passes threshold / ratio; matches1 is not produced.
+extern "C" int fs_float_match_knn(const void* operands, int n_frames, int n_max, const int32_t* counts,
+                                  const int32_t* pair_a, const int32_t* pair_b, int n_pairs, float scale,
+                                  float threshold, float ratio, int32_t* matches0, float* score0, float* second0,
+                                  int32_t* n_matches, int32_t* diag, void* workspace, size_t workspace_bytes,
+                                  fs_stream_t stream_) {
+    return float_match_impl(operands, n_frames, n_max, counts, pair_a, pair_b, n_pairs, scale, threshold, ratio, 0,
+                            matches0, score0, second0, nullptr, n_matches, diag, workspace, workspace_bytes, stream_);
 }

@@ -140,6 +140,13 @@ int fs_float_match(const void* operands_fp16, int n_frames, int n_max, const int
                    int32_t* matches0, float* score0, float* second0, int32_t* matches1,
                    int32_t* n_matches, int32_t* diag,
                    void* workspace, size_t workspace_bytes, fs_stream_t stream);
+/* the same without the mutual check: BFMatcher(NORM_L2).knnMatch(k = 2) + Lowe ratio as ORB_SLAM3/src/Frame.cc:1144-1151
+ * uses it (best / runner-up per query row, strict d_best < ratio * d_second); matches1 is not produced */
+int fs_float_match_knn(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
+                       const int32_t* pair_a, const int32_t* pair_b, int n_pairs,
+                       float scale, float threshold, float ratio,
+                       int32_t* matches0, float* score0, float* second0, int32_t* n_matches, int32_t* diag,
+                       void* workspace, size_t workspace_bytes, fs_stream_t stream);
 /* measurement hook: only the tensor-core kernel of fs_float_match (top-3 keys into the workspace).
  * probe = 0: the real kernel; bit 0: issue no MMAs; bit 1: skip the top-3 network (pipe-overlap experiments);
  * trace: NULL, or 160 x i64 on the device: clock64() at the pipeline's hand-over points of the CTA of pair probe >> 8 */

@@ -250,3 +250,30 @@ def test_gather_matches(fsb):
         assert nc[p] == mk0.shape[0]
         assert np.array_equal(r["mkpts0"][p, :nc[p]].cpu().numpy(), mk0)
         assert np.array_equal(r["mkpts1"][p, :nc[p]].cpu().numpy(), mk1)
+
+
+def test_float_knn_ratio_without_cross_check(fsb):
+    """BFMatcher(NORM_L2, crossCheck=False): best train per query (+ Lowe ratio) without the mutual check
+    (ORB_SLAM3/src/Frame.cc:1144-1151 semantics for float descriptors) against cv2's knnMatch."""
+    import cv2
+    d0, d1 = util.float_descriptors(700, 900, 11)
+    a, b = np.ascontiguousarray(d0.T), np.ascontiguousarray(d1.T)
+    knn = cv2.BFMatcher(cv2.NORM_L2).knnMatch(a, b, k=2)
+    S = d0.T.astype(np.float64) @ d1.astype(np.float64)
+    top = np.sort(S, axis=1)
+    safe = (top[:, -1] - top[:, -2]) > 1e-5               # rows whose arg-max is not a numerical tie
+    got = {m.queryIdx: m.trainIdx for m in fsb.BFMatcher(fsb.NORM_L2, crossCheck=False).match(a, b)}
+    assert len(got) == 700
+    for q, pair in enumerate(knn):
+        if safe[q]:
+            assert got[q] == pair[0].trainIdx
+    ratio = 0.8
+    got_r = {m.queryIdx: m.trainIdx for m in fsb.BFMatcher(fsb.NORM_L2, crossCheck=False).ratioMatch(a, b, ratio)}
+    dist = np.sqrt(np.maximum(0.0, 2.0 - 2.0 * top[:, -2:]))   # [second, best] distances
+    clear = safe & (np.abs(dist[:, 1] - ratio * dist[:, 0]) > 1e-4)
+    for q, pair in enumerate(knn):
+        if clear[q]:
+            assert (q in got_r) == bool(pair[0].distance < ratio * pair[1].distance), q
+            if q in got_r:
+                assert got_r[q] == pair[0].trainIdx
+    assert 50 < len(got_r) < 700
