@@ -751,7 +751,10 @@ def match_mutual_nn(descriptors0, descriptors1, *, scale: float = 1.0, threshold
     """Tail of SuperGlue.forward on the raw contraction (superglue.py:259-260, :268-278).
 
     descriptors0 [256, N0], descriptors1 [256, N1] float32 (SuperPoint layout) →
-    dict(matches0, matches1, matching_scores0, matching_scores1) with -1 for unmatched, like the reference."""
+    dict(matches0, matches1, matching_scores0, matching_scores1) with -1 for unmatched, like the reference.
+    RAW-SCORE CONVENTION (differs from SuperGlue's output dict): `threshold` is compared with the scaled score itself and
+    matching_scores are the scaled scores, not exp(score); a caller replacing superglue.py:273-278 passes
+    threshold=log(match_threshold) (bench.py: log 0.2) and applies exp() to the scores it keeps."""
     dev = _dev()
     d0 = np.asarray(descriptors0, dtype=np.float32)
     d1 = np.asarray(descriptors1, dtype=np.float32)

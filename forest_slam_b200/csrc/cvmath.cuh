@@ -1,4 +1,5 @@
 // cvmath.cuh — device restatements of the small OpenCV numerical building blocks the RANSAC / pose
+// (a restatement of OpenCV arithmetic — OpenCV is Apache-2.0 licensed, (C) its contributors; nothing here is taken from /root/reference)
 // kernels need: cv::RNG (multiply-with-carry), the one-sided Jacobi SVD of core/lapack.cpp including
 // its deterministic completion of missing singular vectors, cv::solvePoly's Durand-Kerner iteration,
 // RANSACUpdateNumIters, Rodrigues.  OpenCV is a third-party dependency of the reference that is not

@@ -1,4 +1,5 @@
 // epnp.cuh — host+device restatement of the minimal solver inside
+// (a restatement of OpenCV arithmetic — OpenCV is Apache-2.0 licensed, (C) its contributors; nothing here is taken from /root/reference)
 //   cv2.solvePnPRansac(points3D, mkpts1_l, K0, dist_coeffs_l, reprojectionError=1.0, confidence=0.99,
 //                      iterationsCount=1000, flags=cv2.SOLVEPNP_ITERATIVE)              stereo_slam.py:294-295
 // OpenCV runs its RANSAC kernel with SOLVEPNP_EPNP on 5-point subsets (calib3d/solvepnp.cpp): the image points are

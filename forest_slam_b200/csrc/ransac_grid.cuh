@@ -355,7 +355,7 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
         int dev = 0;
         if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
         if (!hinted[dev]) {
-            if (Pol::SOLVE_SMEM_DOUBLES == 0)
+            if (Pol::SOLVE_SMEM_DOUBLES == 0 && tune("FS_TUNE_CARVEOUT", 1) == 1)
                 FS_CUDA(cudaFuncSetAttribute(k_rg_solve<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
             hinted[dev] = true;
         }
