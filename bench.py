@@ -39,6 +39,7 @@ if ROOT not in sys.path:
 METRIC = "frame-pairs/sec (match+RANSAC+triangulate)"
 UNIT = "frame-pairs/s"
 LN_THRESH = math.log(0.2)  # superglue.py:275 exp(score) > 0.2 on the scaled score
+SEQ_PAIRS = 256            # frame pairs per synthetic sequence (a batch of more pairs is made of several sequences)
 
 
 def parse_args():
@@ -77,11 +78,23 @@ def make_workload(args, rank: int):
     world = synth.make_world(synth.SEED0)
     # every observation is a gross positional outlier with probability 0.1 => ~19 % corrupted matches per pair
     # (mono = BASELINE config 2, a RANSAC benchmark; the stereo sequence of config 1 is left as generated)
-    frames = synth.make_sequence(args.pairs + 1, n_kpts, seed=synth.SEED0 + 1000 * rank, world=world,
-                                 pos_outlier=pos_outlier(args))
+    # a step's batch = consecutive frame pairs of one or more independent sequences (SEQ_PAIRS pairs each: the forest is
+    # 80 m deep and the rig moves 0.13 m per frame, so one sequence stays inside it for ~450 frames)
+    frames, pair_a, pair_b = [], [], []
+    left, k = args.pairs, 0
+    while left > 0:
+        n = min(left, SEQ_PAIRS)
+        base = len(frames)
+        frames += synth.make_sequence(n + 1, n_kpts, seed=synth.SEED0 + 1000 * rank + 37 * k, world=world,
+                                      pos_outlier=pos_outlier(args))
+        pair_a += list(range(base, base + n))
+        pair_b += list(range(base + 1, base + n + 1))
+        left -= n
+        k += 1
     kpts, dbin, df32, disp, counts = synth.stack_frames(frames)
     return {"frames": frames, "kpts": kpts, "desc_bin": dbin, "desc_f32": df32, "disparity": disp, "counts": counts,
-            "n_kpts": n_kpts}
+            "n_kpts": n_kpts, "pair_a": np.array(pair_a, np.int32), "pair_b": np.array(pair_b, np.int32),
+            "n_sequences": k}
 
 
 def pos_outlier(args) -> float:
@@ -95,6 +108,7 @@ def config_dict(args, wl, world_size):
             if args.workload == "mono" else
             "stereo_slam.py temporal matching (256-bit Hamming crossCheck) + depth back-projection + PnP RANSAC")
     return {"workload": name, "kpts_per_frame": int(wl["n_kpts"]), "pairs_per_step_per_gpu": int(args.pairs),
+            "sequences_per_step": int(wl["n_sequences"]),
             "image": "960x600", "gross_outlier_prob_per_observation": pos_outlier(args),
             "sharding": f"frame-pair index over {world_size} rank(s), one all_gather of records",
             "l2": "L2 flushed (256 MB write) between timed iterations; frame bank per step %.0f MB" % (
@@ -103,7 +117,7 @@ def config_dict(args, wl, world_size):
 
 
 def bank_bytes(args, wl):
-    F = args.pairs + 1
+    F = len(wl["frames"])
     n = wl["n_kpts"]
     per = n * 8 + (n * 256 * 4 if args.workload == "mono" else n * 32 + n * 4)
     return F * per
@@ -215,10 +229,10 @@ def cpu_reference(args, wl, n_sample: int, procs: int):
     mono_slam.py:100-118 / stereo_slam.py:232-306) over `n_sample` frame pairs, data-parallel over `procs` processes
     with one library thread each (findEssentialMat / recoverPose / solvePnPRansac are single-threaded in OpenCV)."""
     fr = wl["frames"]
-    n_sample = max(1, min(n_sample, len(fr) - 1))
+    n_sample = max(1, min(n_sample, len(wl["pair_a"])))
     jobs = []
     for i in range(n_sample):
-        a, b = fr[i], fr[i + 1]
+        a, b = fr[wl["pair_a"][i]], fr[wl["pair_b"][i]]
         if args.workload == "mono":
             jobs.append(("mono", (a.kpts, a.desc_f32, b.kpts, b.desc_f32)))
         else:
@@ -304,7 +318,7 @@ def verify_sequence(args, wl, res, procs: int):
     host = {k: v.detach().cpu().numpy() for k, v in res.items() if hasattr(v, "detach")}
     jobs = []
     for i in range(P):
-        a, b = fr[i], fr[i + 1]
+        a, b = fr[wl["pair_a"][i]], fr[wl["pair_b"][i]]
         if args.workload == "mono":
             fa = {"kpts": a.kpts, "desc": a.desc_f32}
             fb = {"kpts": b.kpts, "desc": b.desc_f32}
@@ -496,8 +510,8 @@ def run_sequence(args, ctx: Ctx):
     lib, dev, rank, world = ctx.lib, ctx.dev, ctx.rank, ctx.world
     wl = make_workload(args, rank)
     P = args.pairs
-    pa = torch.arange(0, P, dtype=torch.int32, device=dev)
-    pb = pa + 1
+    pa = torch.from_numpy(wl["pair_a"]).to(dev)
+    pb = torch.from_numpy(wl["pair_b"]).to(dev)
     host = {"kpts": torch.from_numpy(wl["kpts"]).pin_memory(), "counts": torch.from_numpy(wl["counts"]).pin_memory()}
     if args.workload == "mono":
         host["desc_f32"] = torch.from_numpy(wl["desc_f32"]).pin_memory()
