@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--no-verify", action="store_true", help="skip the parity leg (all pairs of the timed sequence "
                                                             "against oracle/cv_literal.py, outside the timed region)")
     ap.add_argument("--keyframes", type=int, default=2000, help="loopclosure: keyframes (config 5: 2000)")
-    ap.add_argument("--pairs", type=int, default=256, help="frame pairs per step per GPU")
+    ap.add_argument("--pairs", type=int, default=512, help="frame pairs per step per GPU (sequences of 256 pairs)")
     ap.add_argument("--kpts", type=int, default=0, help="keypoints per frame (default 2048 mono / 2000 stereo)")
     ap.add_argument("--cpu-sample", type=int, default=0, help="pairs timed for cpu_baseline (0 = auto)")
     ap.add_argument("--exact-fp32", action="store_true", help="CUDA-core fp32 matcher instead of tcgen05")

@@ -373,7 +373,13 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
     int solve_warps = (pool + 31) / 32;
     // E (five-point, fp64-pipe heavy): beyond one solver warp per SM sub-partition the fp64 issue slots are shared and
     // every solve gets slower; P (EPnP: 12x12 Jacobi SVD in local memory, latency bound at 255 registers) takes two
-    solve_warps = min(solve_warps, fs::sm_count() * pl.solve_warps_per_sm);
+    // ... unless round 0 alone has more solves than that many warps have lanes: a thread that runs two solves back to
+    // back doubles the round's latency, a sub-partition that hosts a second warp stretches it by ~1.3x (measured, mono
+    // 512 pairs per step: 4.2 ms with 4 warps per SM, 2.9 ms with 6), so the policy may allow more warps then
+    const int want = (int)(((long long)n_pairs * pl.first_chunk + 31) / 32);
+    const int per_sm = max(pl.solve_warps_per_sm,
+                           min(Pol::SOLVE_WARPS_PER_SM_MAX, (want + fs::sm_count() - 1) / fs::sm_count()));
+    solve_warps = min(solve_warps, fs::sm_count() * (tune(Pol::TUNE_WARPS, 0) > 0 ? pl.solve_warps_per_sm : per_sm));
     const int solve_grid = (solve_warps + SOLVE_THREADS / 32 - 1) / (SOLVE_THREADS / 32);
     const int score_grid = (pool + Pol::SLAB - 1) / Pol::SLAB;
     for (int r = 0; r <= pl.rounds; r++) {
