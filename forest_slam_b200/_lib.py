@@ -79,6 +79,9 @@ SIGNATURES = {
     "fs_recover_pose_workspace_bytes": (C.c_size_t, [C.c_int]),
     "fs_recover_pose": (C.c_int, [ptr, ptr, ptr, ptr, ptr, C.c_int, C.c_int, C.c_double, C.c_double,
                                   C.c_double, C.c_double, ptr, ptr, ptr, ptr, ptr, C.c_size_t, ptr]),
+    "fs_recover_pose_static_max_pairs": (C.c_int, []),
+    "fs_recover_pose_static": (C.c_int, [ptr, ptr, ptr, ptr, ptr, C.c_int, C.c_int, C.c_double, C.c_double,
+                                         C.c_double, C.c_double, ptr, ptr, ptr, ptr, ptr]),
     "fs_solve_pnp_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "fs_solve_pnp_ransac": (C.c_int, [ptr, ptr, ptr, C.c_int, C.c_int, C.POINTER(FSCamera), C.c_double,
                                       C.c_double, C.c_int, C.c_int, ptr, ptr, ptr, ptr, ptr, ptr, ptr, ptr,

@@ -148,3 +148,77 @@ extern "C" int fs_recover_pose(const double* E, const float* mkpts0, const float
     FS_LAUNCH_CHECK("k_rp_resolve");
     return FS_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fs_recover_pose_static: the same three launches with the per-pair scratch (candidate poses + counters) in a
+// file-scope device array instead of a caller workspace, for callers that cannot allocate (CUDA graph capture, serving
+// loops).  No counterpart in the reference.
+// The array is shared by every call on a device and keeps the last call's contents: k_rp_decompose rewrites every field
+// it uses (counters zeroed) for the pairs of the call, so nothing has to be cleared beforehand; calls that overlap on
+// the GPU (different streams) race on it.
+// ---------------------------------------------------------------------------------------------------------------------
+#include <mutex>
+
+namespace {
+
+static_assert(sizeof(RPPair) == 192, "the header documents 192 B of scratch per pair");
+static __device__ __align__(256) RPPair g_rp_static_scratch[FS_RECOVER_POSE_STATIC_MAX_PAIRS];
+
+// In host code `g_rp_static_scratch` is only a stand-in symbol: its device address is looked up once per device, with
+// that device current, and cached.
+int rp_static_scratch(RPPair** out) {
+    static std::mutex mu;
+    static RPPair* addr[64] = {};
+    int dev = 0;
+    FS_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) {
+        fs::set_error("fs_recover_pose_static: device ordinal %d outside the per-device table (64)", dev);
+        return FS_ERR_UNSUPPORTED;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (!addr[dev]) {
+        void* p = nullptr;
+        FS_CUDA(cudaGetSymbolAddress(&p, g_rp_static_scratch));
+        if (!p) {
+            fs::set_error("fs_recover_pose_static: cudaGetSymbolAddress returned a null address");
+            return FS_ERR_CUDA;
+        }
+        addr[dev] = (RPPair*)p;
+    }
+    *out = addr[dev];
+    return FS_OK;
+}
+
+}  // namespace
+
+extern "C" int fs_recover_pose_static_max_pairs(void) { return FS_RECOVER_POSE_STATIC_MAX_PAIRS; }
+
+extern "C" int fs_recover_pose_static(const double* E, const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                                      const int32_t* status_in, int n_pairs, int n_max, double focal, double pp_x,
+                                      double pp_y, double distance_thresh, double* R, double* t, uint8_t* mask,
+                                      int32_t* n_good, fs_stream_t stream_) {
+    cudaStream_t stream = (cudaStream_t)stream_;
+    FS_REQUIRE(n_pairs >= 0 && n_max >= 0, "negative size");
+    if (n_pairs > FS_RECOVER_POSE_STATIC_MAX_PAIRS) {
+        fs::set_error("fs_recover_pose_static: n_pairs %d exceeds the static scratch (%d pairs); use fs_recover_pose "
+                      "with a caller workspace", n_pairs, FS_RECOVER_POSE_STATIC_MAX_PAIRS);
+        return FS_ERR_BAD_ARG;
+    }
+    if (n_pairs == 0) return FS_OK;
+    FS_REQUIRE(n_max >= 1, "n_max must be positive");
+    FS_REQUIRE(E && mkpts0 && mkpts1 && n_corr && R && t && mask && n_good, "null pointer");
+    FS_REQUIRE(focal != 0, "focal must be non-zero");
+    RPPair* ws = nullptr;
+    const int s = rp_static_scratch(&ws);
+    if (s != FS_OK) return s;
+    k_rp_decompose<<<(n_pairs + 127) / 128, 128, 0, stream>>>(E, status_in, n_pairs, ws);
+    FS_LAUNCH_CHECK("k_rp_decompose (static scratch)");
+    dim3 cgrid((n_max + RP_PTS_PER_CTA - 1) / RP_PTS_PER_CTA, n_pairs);
+    k_rp_cheirality<<<cgrid, RP_THREADS, 0, stream>>>(mkpts0, mkpts1, n_corr, n_max, focal, pp_x, pp_y,
+                                                      distance_thresh, ws, mask);
+    FS_LAUNCH_CHECK("k_rp_cheirality (static scratch)");
+    dim3 rgrid((n_max + 255) / 256, n_pairs);
+    k_rp_resolve<<<rgrid, 256, 0, stream>>>(n_corr, n_max, ws, R, t, mask, n_good);
+    FS_LAUNCH_CHECK("k_rp_resolve (static scratch)");
+    return FS_OK;
+}

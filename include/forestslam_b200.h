@@ -324,6 +324,22 @@ int fs_recover_pose(const double* E, const float* mkpts0, const float* mkpts1, c
                     double* R, double* t, uint8_t* mask, int32_t* n_good,
                     void* workspace, size_t workspace_bytes, fs_stream_t stream);
 
+/* fs_recover_pose_static — fs_recover_pose without a caller workspace and without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-pair scratch (candidate
+ * poses + cheirality counters, 192 B per pair) lives in a file-scope `static __device__ __align__(256)` array of
+ * FS_RECOVER_POSE_STATIC_MAX_PAIRS entries (768 KB, held by every GPU that loads the library until the process exits);
+ * its device address is resolved once per device with cudaGetSymbolAddress.  Same arguments, outputs and bits as
+ * fs_recover_pose.  n_pairs > FS_RECOVER_POSE_STATIC_MAX_PAIRS -> FS_ERR_BAD_ARG (use fs_recover_pose).  Calls no
+ * cudaMalloc / cudaFree / allocating library routine.  Every call on a device shares the array (the kernels rewrite
+ * what they read, nothing needs clearing between calls): calls that OVERLAP on the GPU (different streams) race. */
+#define FS_RECOVER_POSE_STATIC_MAX_PAIRS 4096
+int fs_recover_pose_static_max_pairs(void);
+int fs_recover_pose_static(const double* E, const float* mkpts0, const float* mkpts1, const int32_t* n_corr,
+                           const int32_t* status_in, int n_pairs, int n_max,
+                           double focal, double pp_x, double pp_y, double distance_thresh,
+                           double* R, double* t, uint8_t* mask, int32_t* n_good, fs_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------------
  * A7  PnP RANSAC — replaces
  *       _, rvec, tvec, inliers = cv2.solvePnPRansac(points3D, mkpts1_l, K0, dist_coeffs_l,
