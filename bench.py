@@ -724,7 +724,9 @@ def run_sequence(args, ctx: Ctx):
                       "mean_iters": float(res["iters"].float().mean()),
                       "ok_pairs": int((res["status"] == 0).sum()),
                       **({"matcher_rows_rescanned_exactly": int(res["match_diag"][0]),
-                          "matcher_rows_with_rescored_candidates": int(res["match_diag"][1])}
+                          "matcher_rows_with_rescored_candidates": int(res["match_diag"][1]),
+                          "matcher_columns_with_rescored_slabs": int(res["match_diag"][2]),
+                          "matcher_columns_rescanned_exactly": int(res["match_diag"][3])}
                          if "match_diag" in res else {})}}
     procs = os.cpu_count() or 1
     if not args.no_cpu_baseline:
@@ -779,7 +781,9 @@ def run_float4096(args, ctx: Ctx):
         out[name] = {"ms_per_launch": ms, "pairs_per_s": P / ms * 1e3, "tflops": flop / ms / 1e9,
                      "frac_of_bf16_burst": flop / ms / 1e9 / ctx.peaks["bf16_tflops"],
                      "mean_matches": float(r["n_matches"].float().mean()),
-                     "rows_rescanned_exactly": int(r["diag"][0]) if "diag" in r else None}
+                     "rows_rescanned_exactly": int(r["diag"][0]) if "diag" in r else None,
+                     "columns_with_rescored_slabs": int(r["diag"][2]) if "diag" in r else None,
+                     "columns_rescanned_exactly": int(r["diag"][3]) if "diag" in r else None}
         if name == "forest" and not args.no_verify:
             from oracle import cv_literal as lit
             mis = amb = 0

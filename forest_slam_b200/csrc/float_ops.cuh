@@ -104,6 +104,6 @@ int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMa
 // (three largest 32-column-chunk maxima, largest chunk runner-up), each key = score bits << 12 | (4095 - column)
 int launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max,
                       const int32_t* counts, const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys,
-                      cudaStream_t stream, int probe = 0, long long* trace = nullptr);
+                      cudaStream_t stream, int probe = 0, long long* trace = nullptr, uint32_t* colraw = nullptr);
 
 }  // namespace fs

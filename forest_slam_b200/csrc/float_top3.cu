@@ -55,6 +55,9 @@ struct T3Barriers {
     uint32_t pad;
 };
 constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_BOX_BYTES + 256 /*barriers*/;
+// single-pass variant: per epilogue warp two staging buffers of 32 rows x 32 packed 16-bit scores (2 KB each)
+constexpr int T3_STAGE_BYTES = 32 * 64;
+constexpr int T3_SP_SMEM_BYTES = T3_SMEM_BYTES + 8 * 2 * T3_STAGE_BYTES;
 
 // (best, runner-up) of two disjoint key sets from their (best, runner-up): 3 ops
 __device__ __forceinline__ void top2_merge(uint32_t& h, uint32_t& s, uint32_t h2, uint32_t s2) {
@@ -79,6 +82,15 @@ __device__ __forceinline__ void chunk_top2(const uint32_t (&e)[32], uint32_t& be
     second = s[0];
 }
 
+__device__ __forceinline__ void sts128(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};\n" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+    uint32_t v;
+    asm volatile("ld.shared.b32 %0, [%1];\n" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+
 // insert one key into the running sorted triple (k1 >= k2 >= k3): 5 ops
 __device__ __forceinline__ void top3_insert(uint32_t& k1, uint32_t& k2, uint32_t& k3, uint32_t e) {
     const uint32_t t1 = min(k1, e);
@@ -93,11 +105,25 @@ __device__ __forceinline__ void top3_insert(uint32_t& k1, uint32_t& k2, uint32_t
 // halves (measured before: with MMAs and epilogue switched off the kernel ran at 13.7 TB/s, the L2 cap, so the real
 // kernel queued behind its own loads).  A ring stage is free when BOTH CTAs' MMAs have read it: tcgen05.commit
 // arrives on both CTAs' empty barriers (count 2).
+//
+// SP = true is the SINGLE-PASS form (fs_float_match with the mutual check): only direction 0 runs (half the MMAs), and the
+// column side of superglue.py:268 is reduced inside the epilogue.  Every epilogue warp owns a 32 x 32 block of scores per
+// 32-column chunk (thread = row); it packs the top 16 bits of its 32 keys two to a register (PRMT), writes them to a
+// private 2 KB staging tile (STS.128, swizzled, conflict free), and reads the tile back TRANSPOSED (LDS.32: lane = column
+// pair x row parity, 16 rows each).  A tournament of packed 16-bit min / max (VIMNMX.U16x2, VIMNMX3.U16x2: two columns
+// per instruction, 1.2 ALU operations per score) gives, per column, the best and the runner-up VALUE over a "slab" of 16
+// rows (the rows of one parity inside a 32-row group).  Slab results go to global memory as they are
+// (colraw [pair][slab][column] = best16 | second16 << 16, 8-byte coalesced stores); k_float_colmerge folds the slabs of a
+// column into (three largest slab maxima with slab ids, largest slab runner-up), and k_float_colcheck decides for every
+// row whether it is the arg-max of its best column — from those keys alone when the gaps prove it, by exact rescoring of
+// at most two slabs (32 rows) when they do not, and by an exact column scan otherwise.
+template <bool SP>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T3_THREADS, 1)
 k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_half,
                 const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
-                uint32_t key_mul, int probe, long long* __restrict__ trace, uint4* __restrict__ keys) {
+                uint32_t key_mul, int probe, long long* __restrict__ trace, uint4* __restrict__ keys,
+                uint32_t* __restrict__ colraw) {
 #define T3_TRACE(slot)                                                                   \
     do {                                                                                 \
         if (trace && blockIdx.x == 0 && blockIdx.z == 0 && (int)blockIdx.y == (probe >> 8)) \
@@ -107,7 +133,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // key_mul = 4096 comes in as an argument so that bits * key_mul + idx stays an IMAD (FMA pipe) instead of being
     // strength-reduced to a shift-add on the ALU pipe, which the top-3 network already saturates
     if (threadIdx.x == 0) T3_TRACE(0);
-    const int p = pair0 + blockIdx.y, dir = blockIdx.z;
+    const int p = pair0 + blockIdx.y, dir = SP ? 0 : blockIdx.z;
     const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
     const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
     const int m0 = blockIdx.x * T3_ROWS;
@@ -225,6 +251,23 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             // k1 >= k2 >= k3: the three largest CHUNK maxima (each from a different 32-column chunk, column in the low
             // bits); ks: the largest chunk runner-up.  Every column other than those of k1, k2, k3 scores <= max(k3, ks).
             uint32_t k1 = 0, k2 = 0, k3 = 0, ks = 0;
+            // ---- single-pass column side: staging addresses (bytes, shared window)
+            // write: row `lane`, 16-byte chunk cc at lane * 64 + ((cc ^ ((lane >> 1) & 3)) << 4)
+            // read : lane = parity * 16 + column pair cp; row 2 m + parity, word cp: chunk (cp >> 2) ^ (m & 3)
+            uint32_t st_base = 0, st_wr = 0, st_rd[4] = {0, 0, 0, 0};
+            uint32_t rowmask = 0xFFFFFFFFu;
+            uint32_t* col_out = nullptr;
+            if constexpr (SP) {
+                st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (2 * T3_STAGE_BYTES);
+                st_wr = lane * 64;
+                const int cp = lane & 15, par = lane >> 4;
+#pragma unroll
+                for (int x = 0; x < 4; x++) st_rd[x] = par * 64 + ((((cp >> 2) ^ x) << 4) | ((cp & 3) << 2));
+                rowmask = (row < n0) ? 0xFFFFFFFFu : 0u;
+                const int slab = ((m0 + half * 128 + quarter * 32) >> 5) * 2 + par;
+                col_out = colraw + ((size_t)p * (n_max >> 4) + slab) * n_max + 2 * cp;
+            }
+            const bool warp_partial = SP && (m0 + half * 128 + quarter * 32 + 31 >= n0);
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
@@ -261,12 +304,52 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 #pragma unroll
                         for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
                     }
+                    uint32_t x[16];
+                    if constexpr (SP) {
+                        // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
+                        uint32_t pk[16];
+#pragma unroll
+                        for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
+                        if (warp_partial) {
+#pragma unroll
+                            for (int j = 0; j < 16; j++) pk[j] &= rowmask;
+                        }
+                        // two buffers: the reads of this one (two chunks ago) are ordered before these writes by the
+                        // __syncwarp of the chunk in between
+                        const uint32_t sbuf = st_base + (c & 1) * T3_STAGE_BYTES;
+#pragma unroll
+                        for (int cc = 0; cc < 4; cc++)
+                            sts128(sbuf + st_wr + ((cc ^ ((lane >> 1) & 3)) << 4), pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2],
+                                   pk[4 * cc + 3]);
+                        __syncwarp();
+                        // transposed read-back; the row tournament below runs while these loads are in flight
+#pragma unroll
+                        for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + st_rd[m & 3] + m * 128);
+                    }
                     uint32_t cb, cs;
                     chunk_top2(e, cb, cs);
                     // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
                     cb -= cb ? (uint32_t)col0 : 0u;
                     top3_insert(k1, k2, k3, cb);
                     ks = max(ks, cs);
+                    if constexpr (SP) {
+                        uint32_t h[8], s2[8];
+#pragma unroll
+                        for (int i = 0; i < 8; i++) {
+                            h[i] = __vmaxu2(x[2 * i], x[2 * i + 1]);
+                            s2[i] = __vminu2(x[2 * i], x[2 * i + 1]);
+                        }
+#pragma unroll
+                        for (int w = 4; w >= 1; w >>= 1)
+#pragma unroll
+                            for (int i = 0; i < w; i++) {
+                                s2[i] = __vimax3_u16x2(__vminu2(h[i], h[i + w]), s2[i], s2[i + w]);
+                                h[i] = __vmaxu2(h[i], h[i + w]);
+                            }
+                        // (best | second << 16) of column 2 cp and of column 2 cp + 1
+                        const uint2 o2 = make_uint2(__byte_perm(h[0], s2[0], 0x5410), __byte_perm(h[0], s2[0], 0x7632));
+                        *reinterpret_cast<uint2*>(col_out + col0) = o2;
+                    }
                 }
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
             }
@@ -302,7 +385,8 @@ struct T3Out {
 __global__ void __launch_bounds__(256)
 k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
-                const uint4* __restrict__ keys, float scale, float threshold, float ratio, T3Out out) {
+                const uint4* __restrict__ keys, float scale, float threshold, float ratio, T3Out out,
+                uint32_t* __restrict__ rowkey) {
     const int p = pair0 + blockIdx.y, dir = blockIdx.z;
     const int row = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
     const int fa = dir ? pair_b[p] : pair_a[p], fb = dir ? pair_a[p] : pair_b[p];
@@ -314,8 +398,11 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
     float v1 = -INFINITY, v2 = -INFINITY, v3 = -INFINITY, v2s = -INFINITY;
     int i1 = 0, i2 = 0;
     bool amb_idx = false, want1 = false, want2 = false, full = false;
+    uint32_t kx = 0, ky = 0;
     if (active) {
         const uint4 k = keys[o];
+        kx = k.x;
+        ky = k.y;
         v1 = fs::key_score(k.x, ps);
         v2 = fs::key_score(k.y, ps);
         // k.x >= k.y >= k.z are chunk maxima, k.w the largest chunk runner-up.  Every column other than i1 and i2
@@ -388,6 +475,132 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
     out.best[o] = b;
     out.second[o] = s;
     out.idx[o] = ib;
+    // single-pass form: the tensor-core key of the chosen column (0 = unknown: the row goes through the exact scan)
+    if (rowkey) rowkey[o] = full ? 0u : (ib == i1 ? kx : ky);
+}
+
+// ------------------------------------------------------------------------------------------------ single pass: columns
+// 16-bit column value (top 16 of the 20 live score bits) -> lower edge of the score interval [v, v + step)
+__device__ __forceinline__ float dec16(uint32_t v16, const fs::PairScale& ps) {
+    if (v16 == 0u) return -INFINITY;
+    return (__uint_as_float(0x3F800000u | (v16 << 4)) - fs::KEY_BIAS) * ps.inv_sc;
+}
+
+// thread = (pair, column): fold the slab results of the column into the three largest slab maxima
+// (value << 16 | 0xFFFF - slab: larger value, then lower slab) and the largest slab runner-up value
+constexpr int CM_UNROLL = 8;
+__global__ void __launch_bounds__(256)
+k_float_colmerge(int n_max, const int32_t* __restrict__ counts, const int32_t* __restrict__ pair_a,
+                 const int32_t* __restrict__ pair_b, int pair0, const uint32_t* __restrict__ colraw,
+                 uint4* __restrict__ colkeys) {
+    const int p = pair0 + blockIdx.y, j = blockIdx.x * 256 + threadIdx.x;
+    const int n0 = min(counts[pair_a[p]], n_max), n1 = min(counts[pair_b[p]], n_max);
+    if (j >= n1) return;
+    const int nsl = ((n0 + 31) >> 5) * 2;
+    const uint32_t* src = colraw + (size_t)p * (n_max >> 4) * n_max + j;
+    uint32_t k1 = 0, k2 = 0, k3 = 0, ks = 0;
+    for (int s0 = 0; s0 < nsl; s0 += CM_UNROLL) {
+        uint32_t x[CM_UNROLL];
+#pragma unroll
+        for (int u = 0; u < CM_UNROLL; u++) x[u] = (s0 + u < nsl) ? __ldg(src + (size_t)(s0 + u) * n_max) : 0u;
+#pragma unroll
+        for (int u = 0; u < CM_UNROLL; u++) {
+            const uint32_t h = x[u] & 0xFFFFu;
+            top3_insert(k1, k2, k3, h ? ((h << 16) | (uint32_t)(0xFFFF - (s0 + u))) : 0u);
+            ks = max(ks, x[u] >> 16);
+        }
+    }
+    colkeys[(size_t)p * n_max + j] = make_uint4(k1, k2, k3, ks);
+}
+
+// thread = (pair, row of frame a): is the row the arg-max of its best column?  Writes idx1[pair][column] = row when it is
+// (idx1 was filled with -1; at most one row of a column can be its arg-max, so there is one writer per element).
+//   certain yes : the row's own 16-bit value IS the column's largest slab maximum, in the row's slab, and that maximum
+//                 beats every other slab maximum and every slab runner-up by more than 2 delta + one 16-bit step;
+//   certain no  : the column's largest value exceeds what the row can possibly score;
+//   otherwise   : the rows of the two best slabs (and the row itself) are rescored exactly; every other row scores below
+//                 the third slab maximum + step + delta; if the exact winner clears that, it decides; else exact scan.
+__global__ void __launch_bounds__(256)
+k_float_colcheck(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
+                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
+                 const uint4* __restrict__ colkeys, const uint32_t* __restrict__ rowkey, T3Out out,
+                 int32_t* __restrict__ idx1, uint32_t* __restrict__ list1) {
+    const int p = pair0 + blockIdx.y;
+    const int row = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
+    const int fa = pair_a[p], fb = pair_b[p];
+    const int n0 = min(counts[fa], n_max), n1 = min(counts[fb], n_max);
+    if ((row & ~31) >= n0 || n1 <= 0) return;  // (warp-uniform)
+    const bool active = row < n0;
+    const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
+    const float step = ps.inv_sc * (1.f / 524288.f);  // 16 key units of 2^-23
+    const float dl = ps.delta * 1.0005f;
+    const size_t o = (size_t)p * n_max + row;
+    int j = 0, sl1 = 0, sl2 = -1, state = 0;  // 0 no, 1 yes, 2 ambiguous
+    float c3 = -INFINITY;
+    if (active) {
+        j = out.idx[o];
+        const float b = out.best[o];
+        const uint32_t rk = rowkey[o];
+        const uint4 K = colkeys[(size_t)p * n_max + j];
+        const float c1 = dec16(K.x >> 16, ps), c2 = dec16(K.y >> 16, ps), cS = dec16(K.w, ps);
+        c3 = dec16(K.z >> 16, ps);
+        sl1 = 0xFFFF - (int)(K.x & 0xFFFFu);
+        if (K.y) sl2 = 0xFFFF - (int)(K.y & 0xFFFFu);
+        const bool known = rk != 0u;
+        const float a_i = fs::key_score(rk, ps);
+        const float ex_hi = (known && b == a_i) ? a_i + dl : b;  // b is exact unless it still is the key's value
+        const int slab_i = (row >> 5) * 2 + (row & 1);
+        if (known && (rk >> 16) == (K.x >> 16) && slab_i == sl1 && c1 - (fmaxf(c2, cS) + step) > 2.f * dl) state = 1;
+        else if (ex_hi < c1 - dl) state = 0;
+        else state = 2;
+        if (state == 1) idx1[(size_t)p * n_max + j] = row;
+    }
+    unsigned jobs = __ballot_sync(0xffffffffu, active && state == 2);
+    if (!jobs) return;
+    if (lane == 0) atomicAdd(out.counters + 2, __popc(jobs));
+    const __half* bank_a = static_cast<const __half*>(operands) + (size_t)fa * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+    const __half* bank_b = static_cast<const __half*>(operands) + (size_t)fb * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+    while (jobs) {
+        const int l = __ffs(jobs) - 1;
+        jobs &= jobs - 1;
+        const int r_ = __shfl_sync(0xffffffffu, row, l), j_ = __shfl_sync(0xffffffffu, j, l);
+        const int a1 = __shfl_sync(0xffffffffu, sl1, l), a2 = __shfl_sync(0xffffffffu, sl2, l);
+        const float bound = __shfl_sync(0xffffffffu, c3, l);
+        const fs::OpRow8 bj = fs::load_op_row(bank_b + (size_t)j_ * fs::OP_ROW_HALFS, lane);
+        float eb = -INFINITY;
+        int ib = 0x7fffffff;
+        // candidates 0..15: slab a1, 16..31: slab a2 (if any), 32: the row itself; eight rows in flight
+        for (int c0 = 0; c0 < 40; c0 += 8) {
+            if (a2 < 0 && c0 >= 16 && c0 < 32) continue;  // (warp-uniform) no second slab
+            int cand[8];
+            fs::OpRow8 ar[8];
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const int c = c0 + u;
+                const int sl = c < 16 ? a1 : a2;
+                int r = (c < 32) ? ((sl >> 1) * 32 + 2 * (c & 15) + (sl & 1)) : r_;
+                if ((c >= 16 && c < 32 && a2 < 0) || c > 32 || r >= n0) r = -1;
+                cand[u] = r;
+                ar[u] = fs::load_op_row(bank_a + (size_t)max(r, 0) * fs::OP_ROW_HALFS, lane);
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u++) {
+                const float e = fs::warp_dot(ar[u], bj);
+                if (cand[u] >= 0 && fs::better(e, cand[u], eb, ib)) {
+                    eb = e;
+                    ib = cand[u];
+                }
+            }
+        }
+        if (lane == 0) {
+            if (eb > bound + step + dl) {  // nobody outside the rescored rows can reach the winner (bound -inf: no others)
+                if (ib == r_) idx1[(size_t)p * n_max + j_] = r_;
+            } else {
+                const int pos = atomicAdd(out.counters + 3, 1);
+                list1[pos] = (1u << 31) | (uint32_t)((size_t)p * n_max + j_);
+            }
+        }
+    }
 }
 
 // exact top-2 over ALL columns for the rows the keys could not decide; one CTA (16 warps) per listed row.  The scan is
@@ -396,13 +609,14 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
 constexpr int FSCAN_WARPS = 16, FSCAN_UNROLL = 8;
 __global__ void __launch_bounds__(FSCAN_WARPS * 32)
 k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
-                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, T3Out out) {
+                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, T3Out out,
+                 const uint32_t* __restrict__ list, const int32_t* __restrict__ list_count) {
     __shared__ float s_best[FSCAN_WARPS], s_second[FSCAN_WARPS];
     __shared__ int s_idx[FSCAN_WARPS];
-    const int count = out.counters[0];
+    const int count = *list_count;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int e = blockIdx.x; e < count; e += gridDim.x) {
-        const uint32_t ent = out.list[e];
+        const uint32_t ent = list[e];
         const int dir = ent >> 31;
         const uint32_t lin = ent & 0x7FFFFFFFu;
         const int p = lin / n_max, row = lin % n_max;
@@ -452,26 +666,43 @@ extern "C" size_t fs_float_operand_bytes(int n_frames, int n_max) {
     return (size_t)n_frames * fs::op_rows(n_max) * fs::OP_ROW_BYTES;
 }
 
+// FS_TUNE_FLOAT_SINGLE_PASS=0 keeps fs_float_match on the two-direction kernel (A/B measurements)
+static bool single_pass_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("FS_TUNE_FLOAT_SINGLE_PASS");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
 extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
     if (n_pairs <= 0 || n_max <= 0) return 256;
-    const size_t n2 = 2 * (size_t)n_pairs * n_max;
+    const size_t n = (size_t)n_pairs * n_max, n2 = 2 * n;
     // keys (16 B) + best, second, idx, list (4 B each) for both directions + counters
-    return fs::align_up(n2 * 16, 256) + 4 * fs::align_up(n2 * 4, 256) + 256 + 256;
+    size_t bytes = fs::align_up(n2 * 16, 256) + 4 * fs::align_up(n2 * 4, 256) + 256 + 256;
+    // single-pass form: row keys of the chosen columns + slab results [pair][n_max / 16 slabs][n_max] (4 B each)
+    bytes += fs::align_up(n * 4, 256) + fs::align_up((size_t)n_pairs * ((n_max + 15) / 16) * n_max * 4, 256);
+    return bytes;
 }
 
 // the tensor-core pass alone: top-3 keys of every row of both directions (also the first stage of the tensor-core
 // Hamming matcher, hamming_tc.cu: +-1 operands make the same kernel an exact integer scorer)
 int fs::launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
                           const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
-                          int probe, long long* trace) {
-    static int granted[64];
-    const int st_ = fs::ensure_dyn_smem(k_float_top3_tc, granted, (size_t)(T3_SMEM_BYTES));
+                          int probe, long long* trace, uint32_t* colraw) {
+    static int granted[64], granted_sp[64];
+    const int st_ = colraw ? fs::ensure_dyn_smem(k_float_top3_tc<true>, granted_sp, (size_t)(T3_SP_SMEM_BYTES))
+                           : fs::ensure_dyn_smem(k_float_top3_tc<false>, granted, (size_t)(T3_SMEM_BYTES));
     if (st_ != FS_OK) return st_;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
-        dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, 2);  // clusters of two along x
-        k_float_top3_tc<<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
-                                                                     p0, 4096u, probe, trace, keys);
+        dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, colraw ? 1 : 2);  // clusters of two along x
+        if (colraw)
+            k_float_top3_tc<true><<<grid, T3_THREADS, T3_SP_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a,
+                                                                                  pair_b, n_pairs, p0, 4096u, probe, trace, keys, colraw);
+        else
+            k_float_top3_tc<false><<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a,
+                                                                                pair_b, n_pairs, p0, 4096u, probe, trace, keys, nullptr);
         FS_LAUNCH_CHECK("k_float_top3_tc");
     }
     return FS_OK;
@@ -492,8 +723,16 @@ extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max,
     if (st == FS_OK) st = fs::encode_operand_map(operands, n_frames, n_max, &tmap_half, 64);
     if (st != FS_OK) return st;
     fs::Carver ws(workspace);
-    return fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs,
-                       ws.take<uint4>(2 * (size_t)n_pairs * n_max), (cudaStream_t)stream_, probe, trace);
+    const size_t n = (size_t)n_pairs * n_max, n2 = 2 * n;
+    uint4* keys = ws.take<uint4>(n2);
+    for (int i = 0; i < 4; i++) ws.take<float>(n2);
+    ws.take<int32_t>(64);
+    ws.take<uint32_t>(n);
+    uint32_t* colraw = ws.take<uint32_t>((size_t)n_pairs * (n_max / 16) * n_max);
+    // probe bit 2: the two-direction kernel even where fs_float_match would run the single-pass form
+    const bool sp = single_pass_enabled() && n_max % 128 == 0 && !(probe & 4);
+    return fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys,
+                                 (cudaStream_t)stream_, probe & 3, trace, sp ? colraw : nullptr);
 }
 
 static int float_match_impl(const void* operands, int n_frames, int n_max, const int32_t* counts,
@@ -530,18 +769,43 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
     out.idx = ws.take<int32_t>(n2);
     out.list = ws.take<uint32_t>(n2);
     out.counters = ws.take<int32_t>(64);
+    uint32_t* rowkey = ws.take<uint32_t>(n);
+    uint32_t* colraw = ws.take<uint32_t>((size_t)n_pairs * (n_max / 16) * n_max);
+    // single pass: direction 0 on the tensor cores, the column side from the slab keys (see k_float_top3_tc<true>)
+    const bool sp = cross_check && single_pass_enabled() && n_max % 128 == 0;
     FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));
-    st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
+    st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream, 0,
+                               nullptr, sp ? colraw : nullptr);
     if (st != FS_OK) return st;
+    uint4* colkeys = keys + n;       // direction 1's key slots
+    int32_t* idx1 = out.idx + n;     // arg-max row of every column (-1: no row has this column as its best)
+    uint32_t* list1 = out.list + n;  // columns that need the exact scan
+    if (sp) FS_CUDA(cudaMemsetAsync(idx1, 0xFF, n * sizeof(int32_t), stream));
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
-        dim3 rgrid((n_max + 255) / 256, np, 2);
+        if (sp) {
+            k_float_colmerge<<<dim3((n_max + 255) / 256, np), 256, 0, stream>>>(n_max, counts, pair_a, pair_b, p0, colraw, colkeys);
+            FS_LAUNCH_CHECK("k_float_colmerge");
+        }
+        dim3 rgrid((n_max + 255) / 256, np, sp ? 1 : 2);
         k_float_resolve<<<rgrid, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, p0, keys, scale,
-                                                   threshold, ratio, out);
+                                                   threshold, ratio, out, sp ? rowkey : nullptr);
         FS_LAUNCH_CHECK("k_float_resolve");
     }
-    k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out);
+    k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out,
+                                                                         out.list, out.counters);
     FS_LAUNCH_CHECK("k_float_fullscan");
+    if (sp) {
+        for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
+            const int np = min(32768, n_pairs - p0);
+            k_float_colcheck<<<dim3((n_max + 255) / 256, np), 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, p0,
+                                                                                colkeys, rowkey, out, idx1, list1);
+            FS_LAUNCH_CHECK("k_float_colcheck");
+        }
+        k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs,
+                                                                             out, list1, out.counters + 3);
+        FS_LAUNCH_CHECK("k_float_fullscan(columns)");
+    }
     if (diag) FS_CUDA(cudaMemcpyAsync(diag, out.counters, 4 * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     fs::FloatRowTop2 d0{out.best, out.second, out.idx};
     return fs::launch_float_finalize(n_max, counts, pair_a, pair_b, n_pairs, d0, out.idx + n, scale, threshold, ratio,
