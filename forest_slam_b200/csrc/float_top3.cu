@@ -100,6 +100,89 @@ __device__ __forceinline__ void top3_insert(uint32_t& k1, uint32_t& k2, uint32_t
     k3 = max(k3, t2);
 }
 
+// per-thread state of the epilogue across the tiles of a row
+struct T3Epi {
+    // k1 >= k2 >= k3: the three largest CHUNK maxima (each from a different 32-column chunk, column in the low bits);
+    // ks: the largest chunk runner-up.  Every column other than those of k1, k2, k3 scores <= max(k3, ks).
+    uint32_t k1, k2, k3, ks;
+    // single-pass column side: staging addresses (bytes, shared window) and the slab's output row
+    uint32_t st_base, st_wr[4], st_rd[4], rowmask;
+    bool warp_partial;
+    uint32_t* col_out;
+};
+
+// one 128-column tile of one row: 4 chunks of 32 columns.  MASK: columns >= n1 may exist in this tile, or (single pass)
+// rows >= n0 in this warp's 32-row group.
+template <bool SP, bool MASK>
+__device__ __forceinline__ void t3_tile(const uint32_t (&rr)[T3_BN], int tile_col0, int n1, float sc, uint32_t key_mul,
+                                        T3Epi& es) {
+#pragma unroll
+    for (int c = 0; c < T3_BN / 32; c++) {
+        const uint32_t* r = rr + c * 32;
+        // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is shifted to
+        // the global column afterwards
+        const int col0 = tile_col0 + c * 32;
+        const int nvalid = n1 - col0;
+        if (MASK && nvalid <= 0) {
+            // (warp-uniform) nothing left in this tile; the slab results of the empty chunk are never read
+            break;
+        }
+        uint32_t e[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++)
+            e[j] = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul + (uint32_t)(4095 - j);
+        if (MASK) {
+#pragma unroll
+            for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
+        }
+        uint32_t x[16];
+        if constexpr (SP) {
+            // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
+            uint32_t pk[16];
+#pragma unroll
+            for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
+            if (MASK) {  // rows >= n0 of the last, partially valid 32-row group
+#pragma unroll
+                for (int j = 0; j < 16; j++) pk[j] &= es.rowmask;
+            }
+            // two buffers: the reads of this one (two chunks ago) are ordered before these writes by the __syncwarp of
+            // the chunk in between
+            const uint32_t sbuf = es.st_base + (c & 1) * T3_STAGE_BYTES;
+#pragma unroll
+            for (int cc = 0; cc < 4; cc++)
+                sts128(sbuf + es.st_wr[cc], pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
+            __syncwarp();
+            // transposed read-back; the row tournament below runs while these loads are in flight
+#pragma unroll
+            for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + es.st_rd[m & 3] + m * 128);
+        }
+        uint32_t cb, cs;
+        chunk_top2(e, cb, cs);
+        // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
+        cb -= cb ? (uint32_t)col0 : 0u;
+        top3_insert(es.k1, es.k2, es.k3, cb);
+        es.ks = max(es.ks, cs);
+        if constexpr (SP) {
+            uint32_t h[8], s2[8];
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                h[i] = __vmaxu2(x[2 * i], x[2 * i + 1]);
+                s2[i] = __vminu2(x[2 * i], x[2 * i + 1]);
+            }
+#pragma unroll
+            for (int w = 4; w >= 1; w >>= 1)
+#pragma unroll
+                for (int i = 0; i < w; i++) {
+                    s2[i] = __vimax3_u16x2(__vminu2(h[i], h[i + w]), s2[i], s2[i + w]);
+                    h[i] = __vmaxu2(h[i], h[i + w]);
+                }
+            // (best | second << 16) of column 2 cp and of column 2 cp + 1
+            const uint2 o2 = make_uint2(__byte_perm(h[0], s2[0], 0x5410), __byte_perm(h[0], s2[0], 0x7632));
+            *reinterpret_cast<uint2*>(es.col_out + col0) = o2;
+        }
+    }
+}
+
 // Two CTAs that own neighbouring 256-row blocks of the same (direction, pair) form a cluster and share the streamed
 // frame: each loads HALF of every [128 x 64] box (64 rows) and multicasts it into both shared memories.  L2 -> SM traffic
 // halves (measured before: with MMAs and epilogue switched off the kernel ran at 13.7 TB/s, the L2 cap, so the real
@@ -248,26 +331,27 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             const int row = m0 + half * 128 + quarter * 32 + lane;
             const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
             const float sc = ps.sc;
-            // k1 >= k2 >= k3: the three largest CHUNK maxima (each from a different 32-column chunk, column in the low
-            // bits); ks: the largest chunk runner-up.  Every column other than those of k1, k2, k3 scores <= max(k3, ks).
-            uint32_t k1 = 0, k2 = 0, k3 = 0, ks = 0;
-            // ---- single-pass column side: staging addresses (bytes, shared window)
-            // write: row `lane`, 16-byte chunk cc at lane * 64 + ((cc ^ ((lane >> 1) & 3)) << 4)
-            // read : lane = parity * 16 + column pair cp; row 2 m + parity, word cp: chunk (cp >> 2) ^ (m & 3)
-            uint32_t st_base = 0, st_wr = 0, st_rd[4] = {0, 0, 0, 0};
-            uint32_t rowmask = 0xFFFFFFFFu;
-            uint32_t* col_out = nullptr;
+            T3Epi es;
+            es.k1 = es.k2 = es.k3 = es.ks = 0;
+            es.st_base = 0;
+            es.rowmask = 0xFFFFFFFFu;
+            es.warp_partial = false;
+            es.col_out = nullptr;
             if constexpr (SP) {
-                st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (2 * T3_STAGE_BYTES);
-                st_wr = lane * 64;
+                // write: row `lane`, 16-byte chunk cc at lane * 64 + ((cc ^ ((lane >> 1) & 3)) << 4)
+                // read : lane = parity * 16 + column pair cp; row 2 m + parity, word cp: chunk (cp >> 2) ^ (m & 3)
+                es.st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (2 * T3_STAGE_BYTES);
                 const int cp = lane & 15, par = lane >> 4;
 #pragma unroll
-                for (int x = 0; x < 4; x++) st_rd[x] = par * 64 + ((((cp >> 2) ^ x) << 4) | ((cp & 3) << 2));
-                rowmask = (row < n0) ? 0xFFFFFFFFu : 0u;
+                for (int x = 0; x < 4; x++) {
+                    es.st_wr[x] = lane * 64 + ((x ^ ((lane >> 1) & 3)) << 4);
+                    es.st_rd[x] = par * 64 + ((((cp >> 2) ^ x) << 4) | ((cp & 3) << 2));
+                }
+                es.rowmask = (row < n0) ? 0xFFFFFFFFu : 0u;
+                es.warp_partial = (m0 + half * 128 + quarter * 32 + 31 >= n0);
                 const int slab = ((m0 + half * 128 + quarter * 32) >> 5) * 2 + par;
-                col_out = colraw + ((size_t)p * (n_max >> 4) + slab) * n_max + 2 * cp;
+                es.col_out = colraw + ((size_t)p * (n_max >> 4) + slab) * n_max + 2 * cp;
             }
-            const bool warp_partial = SP && (m0 + half * 128 + quarter * 32 + 31 >= n0);
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
@@ -286,74 +370,18 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
                 if (probe & 2) {
-                    k1 = max(k1, rr[0] ^ rr[127]);
+                    es.k1 = max(es.k1, rr[0] ^ rr[127]);
                     continue;
                 }
-#pragma unroll
-                for (int c = 0; c < T3_BN / 32; c++) {
-                    const uint32_t* r = rr + c * 32;
-                    // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is
-                    // shifted to the global column afterwards
-                    const int col0 = t * T3_BN + c * 32;
-                    const int nvalid = n1 - col0;
-                    uint32_t e[32];
-#pragma unroll
-                    for (int j = 0; j < 32; j++)
-                        e[j] = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul + (uint32_t)(4095 - j);
-                    if (nvalid < 32) {
-#pragma unroll
-                        for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
-                    }
-                    uint32_t x[16];
-                    if constexpr (SP) {
-                        // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
-                        uint32_t pk[16];
-#pragma unroll
-                        for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
-                        if (warp_partial) {
-#pragma unroll
-                            for (int j = 0; j < 16; j++) pk[j] &= rowmask;
-                        }
-                        // two buffers: the reads of this one (two chunks ago) are ordered before these writes by the
-                        // __syncwarp of the chunk in between
-                        const uint32_t sbuf = st_base + (c & 1) * T3_STAGE_BYTES;
-#pragma unroll
-                        for (int cc = 0; cc < 4; cc++)
-                            sts128(sbuf + st_wr + ((cc ^ ((lane >> 1) & 3)) << 4), pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2],
-                                   pk[4 * cc + 3]);
-                        __syncwarp();
-                        // transposed read-back; the row tournament below runs while these loads are in flight
-#pragma unroll
-                        for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + st_rd[m & 3] + m * 128);
-                    }
-                    uint32_t cb, cs;
-                    chunk_top2(e, cb, cs);
-                    // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
-                    cb -= cb ? (uint32_t)col0 : 0u;
-                    top3_insert(k1, k2, k3, cb);
-                    ks = max(ks, cs);
-                    if constexpr (SP) {
-                        uint32_t h[8], s2[8];
-#pragma unroll
-                        for (int i = 0; i < 8; i++) {
-                            h[i] = __vmaxu2(x[2 * i], x[2 * i + 1]);
-                            s2[i] = __vminu2(x[2 * i], x[2 * i + 1]);
-                        }
-#pragma unroll
-                        for (int w = 4; w >= 1; w >>= 1)
-#pragma unroll
-                            for (int i = 0; i < w; i++) {
-                                s2[i] = __vimax3_u16x2(__vminu2(h[i], h[i + w]), s2[i], s2[i + w]);
-                                h[i] = __vmaxu2(h[i], h[i + w]);
-                            }
-                        // (best | second << 16) of column 2 cp and of column 2 cp + 1
-                        const uint2 o2 = make_uint2(__byte_perm(h[0], s2[0], 0x5410), __byte_perm(h[0], s2[0], 0x7632));
-                        *reinterpret_cast<uint2*>(col_out + col0) = o2;
-                    }
-                }
+                // the ragged last tile (n1 not a multiple of 128) runs a second copy of the chunk code with the column
+                // (and, single pass, row) masks; the hot copy has none (if-converted masks cost 2.5 ALU operations per score inline)
+                if ((t == ntiles - 1 && (n1 & (T3_BN - 1))) || es.warp_partial)
+                    t3_tile<SP, true>(rr, t * T3_BN, n1, sc, key_mul, es);
+                else
+                    t3_tile<SP, false>(rr, t * T3_BN, n1, sc, key_mul, es);
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
             }
-            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(k1, k2, k3, ks);
+            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(es.k1, es.k2, es.k3, es.ks);
         }
     }
     if (threadIdx.x == 0) T3_TRACE(4);
