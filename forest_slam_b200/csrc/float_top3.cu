@@ -40,8 +40,17 @@ constexpr int T3_BN = 128, T3_BK = 64, T3_KCH = FS_FLOAT_DIM / T3_BK;  // 4 k-ch
 constexpr int T3_ROWS = 256;                                          // rows per CTA (two MMA halves of 128)
 constexpr int T3_STAGES = 4;  // one tile; (6 stages with run-time stage indexing measured SLOWER: the MMA issue thread is the
                               // critical path — one tile of MMAs takes as long to issue as to execute — so it gets no extra work)
-constexpr int T3_THREADS = 320;
-constexpr int T3_TMA_WARP = 8, T3_MMA_WARP = 9;  // warps 0..7 are the epilogue
+// Epilogue warps: T3_CSPLIT warps share each 32-row TMEM lane quarter of each half and split the tile's 128 columns
+// (CSPLIT = 2: 16 warps, four per scheduler: the epilogue is a chain of dependent phases (tcgen05.ld -> keys -> staging
+// tile -> transposed read -> tournaments), and two warps per scheduler could not cover each other's latencies).
+#ifndef T3_CSPLIT
+#define T3_CSPLIT 2
+#endif
+constexpr int T3_EPI_WARPS = 8 * T3_CSPLIT;
+constexpr int T3_THREADS = (T3_EPI_WARPS + 2) * 32;
+constexpr int T3_TMA_WARP = T3_EPI_WARPS, T3_MMA_WARP = T3_EPI_WARPS + 1;  // warps below are the epilogue
+constexpr int T3_CW = T3_BN / T3_CSPLIT;     // columns of a tile per epilogue warp
+constexpr int T3_NBUF = T3_CSPLIT == 1 ? 2 : 1;  // staging tiles per warp (single pass)
 constexpr int T3_BOX_BYTES = 128 * T3_BK * 2;               // 16 KB: one [128 x 64] fp16 box
 constexpr int T3_A_BYTES = 2 * T3_KCH * T3_BOX_BYTES;       // 128 KB
 constexpr int T3_TMEM_COLS = 512;
@@ -55,9 +64,9 @@ struct T3Barriers {
     uint32_t pad;
 };
 constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_BOX_BYTES + 256 /*barriers*/;
-// single-pass variant: per epilogue warp two staging buffers of 32 rows x 32 packed 16-bit scores (2 KB each)
+// single-pass variant: per epilogue warp T3_NBUF staging tiles of 32 rows x 32 packed 16-bit scores (2 KB each)
 constexpr int T3_STAGE_BYTES = 32 * 64;
-constexpr int T3_SP_SMEM_BYTES = T3_SMEM_BYTES + 8 * 2 * T3_STAGE_BYTES;
+constexpr int T3_SP_SMEM_BYTES = T3_SMEM_BYTES + T3_EPI_WARPS * T3_NBUF * T3_STAGE_BYTES;
 
 // (best, runner-up) of two disjoint key sets from their (best, runner-up): 3 ops
 __device__ __forceinline__ void top2_merge(uint32_t& h, uint32_t& s, uint32_t h2, uint32_t s2) {
@@ -111,75 +120,68 @@ struct T3Epi {
     uint32_t* col_out;
 };
 
-// one 128-column tile of one row: 4 chunks of 32 columns.  MASK: columns >= n1 may exist in this tile, or (single pass)
-// rows >= n0 in this warp's 32-row group.
+// one chunk of 32 columns of one row (r: its 32 accumulator values).  MASK: columns >= n1 may exist in this chunk, or
+// (single pass) rows >= n0 in this warp's 32-row group.  c: chunk counter (selects the staging tile when there are two).
 template <bool SP, bool MASK>
-__device__ __forceinline__ void t3_tile(const uint32_t (&rr)[T3_BN], int tile_col0, int n1, float sc, uint32_t key_mul,
-                                        T3Epi& es) {
+__device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int c, int n1, float sc, uint32_t key_mul,
+                                         T3Epi& es) {
+    // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is shifted to the
+    // global column afterwards
+    const int nvalid = n1 - col0;
+    if (MASK && nvalid <= 0) return;  // (warp-uniform) the slab results of an empty chunk are never read
+    uint32_t e[32];
 #pragma unroll
-    for (int c = 0; c < T3_BN / 32; c++) {
-        const uint32_t* r = rr + c * 32;
-        // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is shifted to
-        // the global column afterwards
-        const int col0 = tile_col0 + c * 32;
-        const int nvalid = n1 - col0;
-        if (MASK && nvalid <= 0) {
-            // (warp-uniform) nothing left in this tile; the slab results of the empty chunk are never read
-            break;
+    for (int j = 0; j < 32; j++)
+        e[j] = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul + (uint32_t)(4095 - j);
+    if (MASK) {
+#pragma unroll
+        for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
+    }
+    uint32_t x[16];
+    if constexpr (SP) {
+        // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
+        uint32_t pk[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
+        if (MASK) {  // rows >= n0 of the last, partially valid 32-row group
+#pragma unroll
+            for (int j = 0; j < 16; j++) pk[j] &= es.rowmask;
         }
-        uint32_t e[32];
+        // two tiles: the reads of this one (two chunks ago) are ordered before these writes by the __syncwarp of the chunk
+        // in between; one tile: by the __syncwarp here
+        const uint32_t sbuf = es.st_base + (c & (T3_NBUF - 1)) * T3_STAGE_BYTES;
+        if (T3_NBUF == 1) __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 32; j++)
-            e[j] = __float_as_uint(fmaf(__uint_as_float(r[j]), sc, fs::KEY_BIAS)) * key_mul + (uint32_t)(4095 - j);
-        if (MASK) {
+        for (int cc = 0; cc < 4; cc++)
+            sts128(sbuf + es.st_wr[cc], pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
+        __syncwarp();
+        // transposed read-back; the row tournament below runs while these loads are in flight
 #pragma unroll
-            for (int j = 0; j < 32; j++) e[j] = (j < nvalid) ? e[j] : 0u;
+        for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + es.st_rd[m & 3] + m * 128);
+    }
+    uint32_t cb, cs;
+    chunk_top2(e, cb, cs);
+    // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
+    cb -= cb ? (uint32_t)col0 : 0u;
+    top3_insert(es.k1, es.k2, es.k3, cb);
+    es.ks = max(es.ks, cs);
+    if constexpr (SP) {
+        uint32_t h[8], s2[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            h[i] = __vmaxu2(x[2 * i], x[2 * i + 1]);
+            s2[i] = __vminu2(x[2 * i], x[2 * i + 1]);
         }
-        uint32_t x[16];
-        if constexpr (SP) {
-            // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
-            uint32_t pk[16];
 #pragma unroll
-            for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
-            if (MASK) {  // rows >= n0 of the last, partially valid 32-row group
+        for (int w = 4; w >= 1; w >>= 1)
 #pragma unroll
-                for (int j = 0; j < 16; j++) pk[j] &= es.rowmask;
+            for (int i = 0; i < w; i++) {
+                s2[i] = __vimax3_u16x2(__vminu2(h[i], h[i + w]), s2[i], s2[i + w]);
+                h[i] = __vmaxu2(h[i], h[i + w]);
             }
-            // two buffers: the reads of this one (two chunks ago) are ordered before these writes by the __syncwarp of
-            // the chunk in between
-            const uint32_t sbuf = es.st_base + (c & 1) * T3_STAGE_BYTES;
-#pragma unroll
-            for (int cc = 0; cc < 4; cc++)
-                sts128(sbuf + es.st_wr[cc], pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
-            __syncwarp();
-            // transposed read-back; the row tournament below runs while these loads are in flight
-#pragma unroll
-            for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + es.st_rd[m & 3] + m * 128);
-        }
-        uint32_t cb, cs;
-        chunk_top2(e, cb, cs);
-        // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
-        cb -= cb ? (uint32_t)col0 : 0u;
-        top3_insert(es.k1, es.k2, es.k3, cb);
-        es.ks = max(es.ks, cs);
-        if constexpr (SP) {
-            uint32_t h[8], s2[8];
-#pragma unroll
-            for (int i = 0; i < 8; i++) {
-                h[i] = __vmaxu2(x[2 * i], x[2 * i + 1]);
-                s2[i] = __vminu2(x[2 * i], x[2 * i + 1]);
-            }
-#pragma unroll
-            for (int w = 4; w >= 1; w >>= 1)
-#pragma unroll
-                for (int i = 0; i < w; i++) {
-                    s2[i] = __vimax3_u16x2(__vminu2(h[i], h[i + w]), s2[i], s2[i + w]);
-                    h[i] = __vmaxu2(h[i], h[i + w]);
-                }
-            // (best | second << 16) of column 2 cp and of column 2 cp + 1
-            const uint2 o2 = make_uint2(__byte_perm(h[0], s2[0], 0x5410), __byte_perm(h[0], s2[0], 0x7632));
-            *reinterpret_cast<uint2*>(es.col_out + col0) = o2;
-        }
+        // (best | second << 16) of column 2 cp and of column 2 cp + 1
+        const uint2 o2 = make_uint2(__byte_perm(h[0], s2[0], 0x5410), __byte_perm(h[0], s2[0], 0x7632));
+        *reinterpret_cast<uint2*>(es.col_out + col0) = o2;
     }
 }
 
@@ -243,7 +245,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(&bar.tmem_full[b], 1);
-            mbar_init(&bar.tmem_empty[b], 4 * nhalf);
+            mbar_init(&bar.tmem_empty[b], 4 * T3_CSPLIT * nhalf);
         }
         fence_barrier_init();
     }
@@ -257,76 +259,93 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     const uint32_t tmem_base = bar.tmem_base;
     if (threadIdx.x == 0) T3_TRACE(1);
 
+    // The TMA and the MMA warp run their loops CONVERGED (all 32 lanes wait on the barriers) and elect one lane only for the
+    // asynchronous instructions themselves: in warp-uniform control flow the compiler keeps the loop state, addresses and
+    // descriptors in uniform registers, so a tcgen05.mma is one instruction.  (Under `if (lane == 0)` every UTCHMMA /
+    // UTMALDG sat in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop of ~13 dependent instructions: the MMA warp took as long
+    // to issue a tile as the tensor pipe took to execute it, and any competition for its issue slots slowed the pipe.)
     if (warp == T3_TMA_WARP) {
-        // ===================================================== TMA producer (one thread)
-        if (lane == 0 && ntiles > 0) {
-            if (!ghost) {
+        // ===================================================== TMA producer
+        if (ntiles > 0) {
+            if (!ghost && elect_one()) {
                 mbar_arrive_expect_tx(&bar.a_full, nhalf * T3_KCH * T3_BOX_BYTES);
                 for (int h = 0; h < nhalf; h++)
                     for (int kc = 0; kc < T3_KCH; kc++)
                         tma_load_3d(sA + (h * T3_KCH + kc) * T3_BOX_BYTES, &tmap, &bar.a_full, kc * T3_BK, m0 + h * 128, fa);
             }
+            __syncwarp();
             int it = 0;
             for (int t = 0; t < ntiles; t++) {
+#pragma unroll
                 for (int kc = 0; kc < T3_KCH; kc++, it++) {
                     const int s = it % T3_STAGES;
                     mbar_wait(&bar.empty[s], ((it / T3_STAGES) & 1) ^ 1);
-                    mbar_arrive_expect_tx(&bar.full[s], T3_BOX_BYTES);  // own half + the peer's half
-                    tma_load_3d_multicast(sB + s * T3_BOX_BYTES + rank * (T3_BOX_BYTES / 2), &tmap_half, &bar.full[s],
-                                          kc * T3_BK, t * T3_BN + (int)rank * 64, fb, (uint16_t)3);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&bar.full[s], T3_BOX_BYTES);  // own half + the peer's half
+                        tma_load_3d_multicast(sB + s * T3_BOX_BYTES + rank * (T3_BOX_BYTES / 2), &tmap_half, &bar.full[s],
+                                              kc * T3_BK, t * T3_BN + (int)rank * 64, fb, (uint16_t)3);
+                    }
+                    __syncwarp();
                 }
-                if (t < 20) T3_TRACE(10 + t);
+                if (lane == 0 && t < 20) T3_TRACE(10 + t);
             }
         }
     } else if (warp == T3_MMA_WARP) {
-        // ===================================================== MMA issuer (one thread).  This warp has the highest warp id
-        // of the CTA: the sub-partition's arbiter prefers it over the two epilogue warps it shares issue slots with, so
-        // the tensor pipe is never starved by the ALU-bound epilogue (measured: with the issuer as warp 1 the MMAs and
-        // the epilogue of consecutive tiles ran back to back instead of overlapped).
-        if (lane == 0 && ntiles > 0 && ghost) {
+        // ===================================================== MMA issuer.  This warp has the highest warp id of the CTA:
+        // the sub-partition's arbiter prefers it over the epilogue warps it shares issue slots with, so the tensor pipe is
+        // never starved by the ALU-bound epilogue (measured: with the issuer as warp 1 the MMAs and the epilogue of
+        // consecutive tiles ran back to back instead of overlapped).
+        if (ntiles > 0 && ghost) {
             for (int it = 0; it < ntiles * T3_KCH; it++) {
                 const int s = it % T3_STAGES;
                 mbar_wait(&bar.full[s], (it / T3_STAGES) & 1);
-                umma_commit_multicast(&bar.empty[s], (uint16_t)3);
+                if (elect_one()) umma_commit_multicast(&bar.empty[s], (uint16_t)3);
+                __syncwarp();
             }
-        } else if (lane == 0 && ntiles > 0) {
+        } else if (ntiles > 0) {
             mbar_wait(&bar.a_full, 0);
             tc_fence_after();
-            T3_TRACE(3);
+            if (lane == 0) T3_TRACE(3);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);  // (tells the compiler it is warp-uniform)
             const uint64_t a_desc0 = make_desc_k_sw128(smem_u32(sA)), b_desc0 = make_desc_k_sw128(smem_u32(sB));
             int it = 0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_empty[buf], ((t >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t d0 = tmem_base + (buf * 2) * T3_BN;
-                if (t < 20) T3_TRACE(30 + t);
+                const uint32_t d0 = tmem_u + (buf * 2) * T3_BN;
+                if (lane == 0 && t < 20) T3_TRACE(30 + t);
 #pragma unroll
                 for (int kc = 0; kc < T3_KCH; kc++, it++) {
                     const int s = it % T3_STAGES;
                     mbar_wait(&bar.full[s], (it / T3_STAGES) & 1);
                     tc_fence_after();
                     const uint64_t bs = b_desc0 + (uint64_t)((s * T3_BOX_BYTES) >> 4);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int ks = 0; ks < T3_BK / 16; ks++) {
-                        // descriptor start-address field is in 16-byte units: +2 per K = 16 step inside the swizzle row
-                        const uint64_t bd = bs + (uint64_t)((ks * 32) >> 4);
-                        const uint64_t ad = a_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
-                        if (probe & 1) continue;
-                        umma_f16(d0, ad, bd, T3_IDESC, (kc | ks) != 0);
-                        if (nhalf == 2)
-                            umma_f16(d0 + T3_BN, ad + (uint64_t)((T3_KCH * T3_BOX_BYTES) >> 4), bd, T3_IDESC, (kc | ks) != 0);
+                        for (int ks = 0; ks < T3_BK / 16; ks++) {
+                            // descriptor start-address field is in 16-byte units: +2 per K = 16 step inside the swizzle row
+                            const uint64_t bd = bs + (uint64_t)((ks * 32) >> 4);
+                            const uint64_t ad = a_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                            if (probe & 1) continue;
+                            umma_f16(d0, ad, bd, T3_IDESC, (kc | ks) != 0);
+                            if (nhalf == 2)
+                                umma_f16(d0 + T3_BN, ad + (uint64_t)((T3_KCH * T3_BOX_BYTES) >> 4), bd, T3_IDESC, (kc | ks) != 0);
+                        }
+                        umma_commit_multicast(&bar.empty[s], (uint16_t)3);  // ring stage read (here); the peer adds its own
                     }
-                    umma_commit_multicast(&bar.empty[s], (uint16_t)3);  // ring stage read (here); the peer adds its own
+                    __syncwarp();
                 }
-                umma_commit(&bar.tmem_full[buf]);  // both accumulators of this tile complete
-                if (t < 20) T3_TRACE(50 + t);
+                if (elect_one()) umma_commit(&bar.tmem_full[buf]);  // both accumulators of this tile complete
+                __syncwarp();
+                if (lane == 0 && t < 20) T3_TRACE(50 + t);
             }
         }
     } else {
         // ===================================================== epilogue: warps 0..7, thread = row
-        const int half = warp >> 2;
+        const int half = (warp >> 2) & 1;
         const int quarter = warp & 3;  // the TMEM lane quarter this warp may read
+        const int csp = warp >> 3;     // which T3_CW columns of every tile
         if (half < nhalf && !ghost) {
             const int row = m0 + half * 128 + quarter * 32 + lane;
             const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
@@ -340,7 +359,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             if constexpr (SP) {
                 // write: row `lane`, 16-byte chunk cc at lane * 64 + ((cc ^ ((lane >> 1) & 3)) << 4)
                 // read : lane = parity * 16 + column pair cp; row 2 m + parity, word cp: chunk (cp >> 2) ^ (m & 3)
-                es.st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (2 * T3_STAGE_BYTES);
+                es.st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (T3_NBUF * T3_STAGE_BYTES);
                 const int cp = lane & 15, par = lane >> 4;
 #pragma unroll
                 for (int x = 0; x < 4; x++) {
@@ -357,31 +376,71 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
                 tc_fence_after();
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(70 + t);
-                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN;
-                // the whole 128-column accumulator row goes to registers at once, and the TMEM buffer is handed back to
-                // the MMA warp BEFORE the top-3 network runs: the next-but-one tile's MMAs never wait for this warp's ALU
-                // work (measured: releasing after the last chunk's load left both pipes idle ~20 % of the time)
-                uint32_t rr[T3_BN];
+                const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN + csp * T3_CW;
+                // the ragged last tile (n1 not a multiple of 128) and the last, partially valid row group run a second copy
+                // of the chunk code with the column (and, single pass, row) masks; the hot copy has none (if-converted
+                // masks cost 2.5 ALU operations per score inline)
+                const bool masked = (t == ntiles - 1 && (n1 & (T3_BN - 1))) || es.warp_partial;
+                const int tcol0 = t * T3_BN + csp * T3_CW;
+                if constexpr (T3_CSPLIT == 1) {
+                    // the whole 128-column accumulator row goes to registers at once, and the TMEM buffer is handed back
+                    // to the MMA warp BEFORE the top-3 network runs
+                    uint32_t rr[T3_CW / 32][32];
 #pragma unroll
-                for (int c = 0; c < T3_BN / 32; c++) tmem_ld_32x32b_x32(taddr + c * 32, rr + c * 32);
-                tmem_ld_wait();
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
-                if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
-                if (probe & 2) {
-                    es.k1 = max(es.k1, rr[0] ^ rr[127]);
-                    continue;
+                    for (int c = 0; c < T3_CW / 32; c++) tmem_ld_32x32b_x32(taddr + c * 32, rr[c]);
+                    tmem_ld_wait();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                    if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
+                    if (probe & 2) {
+                        es.k1 = max(es.k1, rr[0][0] ^ rr[T3_CW / 32 - 1][31]);
+                        continue;
+                    }
+#pragma unroll
+                    for (int c = 0; c < T3_CW / 32; c++) {
+                        if (masked) t3_chunk<SP, true>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        else t3_chunk<SP, false>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
+                    }
+                } else {
+                    // chunk by chunk (the register budget of 18 warps): the buffer goes back after the last chunk's load
+                    uint32_t rr[32];
+#pragma unroll
+                    for (int c = 0; c < T3_CW / 32; c++) {
+                        tmem_ld_32x32b_x32(taddr + c * 32, rr);
+                        tmem_ld_wait();
+                        if (c == T3_CW / 32 - 1) {
+                            tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                            if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
+                        }
+                        if (probe & 2) {
+                            es.k1 = max(es.k1, rr[0] ^ rr[31]);
+                            continue;
+                        }
+                        if (masked) t3_chunk<SP, true>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        else t3_chunk<SP, false>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
+                    }
                 }
-                // the ragged last tile (n1 not a multiple of 128) runs a second copy of the chunk code with the column
-                // (and, single pass, row) masks; the hot copy has none (if-converted masks cost 2.5 ALU operations per score inline)
-                if ((t == ntiles - 1 && (n1 & (T3_BN - 1))) || es.warp_partial)
-                    t3_tile<SP, true>(rr, t * T3_BN, n1, sc, key_mul, es);
-                else
-                    t3_tile<SP, false>(rr, t * T3_BN, n1, sc, key_mul, es);
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
             }
-            if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(es.k1, es.k2, es.k3, es.ks);
+            if constexpr (T3_CSPLIT == 1) {
+                if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(es.k1, es.k2, es.k3, es.ks);
+            } else {
+                // the warps of a row group merge their column ranges: the upper ones park their keys in shared memory
+                uint4* park = reinterpret_cast<uint4*>(sA) + (warp & 7) * 32 + lane;  // the row block is dead: every MMA is done
+                if (csp > 0) *park = make_uint4(es.k1, es.k2, es.k3, es.ks);
+                named_bar_sync(1 + (warp & 7), 64);
+                if (csp == 0) {
+                    const uint4 o = *park;
+                    top3_insert(es.k1, es.k2, es.k3, o.x);
+                    top3_insert(es.k1, es.k2, es.k3, o.y);
+                    top3_insert(es.k1, es.k2, es.k3, o.z);
+                    es.ks = max(es.ks, o.w);
+                    if (row < n0) keys[((size_t)dir * n_pairs_total + p) * n_max + row] = make_uint4(es.k1, es.k2, es.k3, es.ks);
+                }
+            }
         }
     }
     if (threadIdx.x == 0) T3_TRACE(4);
