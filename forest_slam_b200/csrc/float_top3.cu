@@ -745,6 +745,59 @@ k_float_fullscan(const void* __restrict__ operands, int n_max, const int32_t* __
     }
 }
 
+// Single-pass form: the exact top-2 of a listed ROW without reading the whole other frame.  The slab results bound every
+// tensor-core score of the row from above: S~(row, j) < dec16(best16 of (slab(row), j)) + step.  Two distinct columns are
+// known to score >= t2 := max(second chunk maximum, best chunk runner-up), so a column whose bound is <= t2 - 2 delta
+// cannot be among the exact top two; only the others (a few dozen of thousands, even on random descriptors) are rescored
+// exactly.  One warp per row: 4 B per column read instead of 1 KB.
+__global__ void __launch_bounds__(256)
+k_float_slabscan(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
+                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, const uint4* __restrict__ keys,
+                 const uint32_t* __restrict__ colraw, T3Out out, const uint32_t* __restrict__ list,
+                 const int32_t* __restrict__ list_count) {
+    const int count = *list_count;
+    const int lane = threadIdx.x & 31;
+    const int nwarps = gridDim.x * 8;
+    for (int e = blockIdx.x * 8 + (threadIdx.x >> 5); e < count; e += nwarps) {
+        const uint32_t lin = list[e] & 0x7FFFFFFFu;  // direction 0 only
+        const int p = lin / n_max, row = lin % n_max;
+        const int fa = pair_a[p], fb = pair_b[p];
+        const int n1 = min(counts[fb], n_max);
+        const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
+        const float step = ps.inv_sc * (1.f / 524288.f), dl = ps.delta * 1.0005f;
+        const uint4 K = keys[(size_t)p * n_max + row];
+        const float thr = fmaxf(fs::key_score(K.y, ps), fs::key_score(K.w, ps)) - 2.f * dl - step;  // -inf: one column
+        const __half* bank_a = static_cast<const __half*>(operands) + (size_t)fa * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+        const __half* bank_b = static_cast<const __half*>(operands) + (size_t)fb * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
+        const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)row * fs::OP_ROW_HALFS, lane);
+        const uint32_t* src = colraw + ((size_t)p * (n_max >> 4) + ((row >> 5) * 2 + (row & 1))) * n_max;
+        fs::Top2 t;
+        t.init();
+        for (int j0 = 0; j0 < n1; j0 += 128) {
+            uint32_t x[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) x[u] = (j0 + u * 32 + lane < n1) ? __ldg(src + j0 + u * 32 + lane) : 0u;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const bool cand = (j0 + u * 32 + lane < n1) && !(dec16(x[u] & 0xFFFFu, ps) <= thr);
+                unsigned m = __ballot_sync(0xffffffffu, cand);
+                while (m) {  // ascending columns
+                    const int j = j0 + u * 32 + __ffs(m) - 1;
+                    m &= m - 1;
+                    const float v = fs::warp_dot(a, fs::load_op_row(bank_b + (size_t)j * fs::OP_ROW_HALFS, lane));
+                    t.push(v, j);
+                }
+            }
+        }
+        if (lane == 0) {
+            const size_t o = (size_t)p * n_max + row;
+            out.best[o] = t.best;
+            out.second[o] = t.second;
+            out.idx[o] = t.idx;
+        }
+    }
+}
+
 }  // namespace
 
 // ------------------------------------------------------------------------------------------------ C ABI
@@ -879,9 +932,15 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
                                                    threshold, ratio, out, sp ? rowkey : nullptr);
         FS_LAUNCH_CHECK("k_float_resolve");
     }
-    k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, out,
-                                                                         out.list, out.counters);
-    FS_LAUNCH_CHECK("k_float_fullscan");
+    if (sp) {
+        k_float_slabscan<<<fs::sm_count() * 4, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, keys, colraw, out,
+                                                                 out.list, out.counters);
+        FS_LAUNCH_CHECK("k_float_slabscan");
+    } else {
+        k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs,
+                                                                             out, out.list, out.counters);
+        FS_LAUNCH_CHECK("k_float_fullscan");
+    }
     if (sp) {
         for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
             const int np = min(32768, n_pairs - p0);
