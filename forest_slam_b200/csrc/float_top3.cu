@@ -606,12 +606,13 @@ k_float_colmerge(int n_max, const int32_t* __restrict__ counts, const int32_t* _
 //                 beats every other slab maximum and every slab runner-up by more than 2 delta + one 16-bit step;
 //   certain no  : the column's largest value exceeds what the row can possibly score;
 //   otherwise   : the rows of the two best slabs (and the row itself) are rescored exactly; every other row scores below
-//                 the third slab maximum + step + delta; if the exact winner clears that, it decides; else exact scan.
+//                 the third slab maximum + step + delta; if the exact winner clears that, it decides; else every other
+//                 slab whose maximum could still reach the winner is rescored as well (counters[3]).
 __global__ void __launch_bounds__(256)
 k_float_colcheck(const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
                  const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
-                 const uint4* __restrict__ colkeys, const uint32_t* __restrict__ rowkey, T3Out out,
-                 int32_t* __restrict__ idx1, uint32_t* __restrict__ list1) {
+                 const uint4* __restrict__ colkeys, const uint32_t* __restrict__ rowkey,
+                 const uint32_t* __restrict__ colraw, T3Out out, int32_t* __restrict__ idx1) {
     const int p = pair0 + blockIdx.y;
     const int row = blockIdx.x * 256 + threadIdx.x, lane = threadIdx.x & 31;
     const int fa = pair_a[p], fb = pair_b[p];
@@ -656,37 +657,54 @@ k_float_colcheck(const void* __restrict__ operands, int n_max, const int32_t* __
         const fs::OpRow8 bj = fs::load_op_row(bank_b + (size_t)j_ * fs::OP_ROW_HALFS, lane);
         float eb = -INFINITY;
         int ib = 0x7fffffff;
-        // candidates 0..15: slab a1, 16..31: slab a2 (if any), 32: the row itself; eight rows in flight
-        for (int c0 = 0; c0 < 40; c0 += 8) {
-            if (a2 < 0 && c0 >= 16 && c0 < 32) continue;  // (warp-uniform) no second slab
-            int cand[8];
-            fs::OpRow8 ar[8];
+        // exact scores of the 16 rows of slab sl (the rows of one parity of a 32-row group), eight rows in flight
+        auto rescore_slab = [&](int sl) {
+#pragma unroll 1
+            for (int c0 = 0; c0 < 16; c0 += 8) {
+                int cand[8];
+                fs::OpRow8 ar[8];
 #pragma unroll
-            for (int u = 0; u < 8; u++) {
-                const int c = c0 + u;
-                const int sl = c < 16 ? a1 : a2;
-                int r = (c < 32) ? ((sl >> 1) * 32 + 2 * (c & 15) + (sl & 1)) : r_;
-                if ((c >= 16 && c < 32 && a2 < 0) || c > 32 || r >= n0) r = -1;
-                cand[u] = r;
-                ar[u] = fs::load_op_row(bank_a + (size_t)max(r, 0) * fs::OP_ROW_HALFS, lane);
+                for (int u = 0; u < 8; u++) {
+                    const int r = (sl >> 1) * 32 + 2 * (c0 + u) + (sl & 1);
+                    cand[u] = r < n0 ? r : -1;
+                    ar[u] = fs::load_op_row(bank_a + (size_t)min(r, n0 - 1) * fs::OP_ROW_HALFS, lane);
+                }
+#pragma unroll
+                for (int u = 0; u < 8; u++) {
+                    const float e = fs::warp_dot(ar[u], bj);
+                    if (cand[u] >= 0 && fs::better(e, cand[u], eb, ib)) {
+                        eb = e;
+                        ib = cand[u];
+                    }
+                }
             }
-#pragma unroll
-            for (int u = 0; u < 8; u++) {
-                const float e = fs::warp_dot(ar[u], bj);
-                if (cand[u] >= 0 && fs::better(e, cand[u], eb, ib)) {
-                    eb = e;
-                    ib = cand[u];
+        };
+        {
+            const float e = fs::warp_dot(fs::load_op_row(bank_a + (size_t)r_ * fs::OP_ROW_HALFS, lane), bj);
+            eb = e;
+            ib = r_;
+        }
+        rescore_slab(a1);
+        if (a2 >= 0) rescore_slab(a2);
+        // every row outside the rescored slabs scores below (third slab maximum + step + delta); if the exact winner does
+        // not clear that, the other slabs whose maximum could still reach it are rescored too (their bound comes from
+        // the slab results of this column: 4 B per slab instead of an exact scan of the whole column)
+        if (!(eb > bound + step + dl)) {  // (warp-uniform: eb is the same in every lane)
+            if (lane == 0) atomicAdd(out.counters + 3, 1);
+            const int nsl = ((n0 + 31) >> 5) * 2;
+            const uint32_t* src = colraw + (size_t)p * (n_max >> 4) * n_max + j_;
+            for (int s0 = 0; s0 < nsl; s0 += 32) {
+                const int sl = s0 + lane;
+                const uint32_t h = (sl < nsl) ? (__ldg(src + (size_t)sl * n_max) & 0xFFFFu) : 0u;
+                const bool c = sl < nsl && sl != a1 && sl != a2 && h != 0u && (dec16(h, ps) + step + dl > eb);
+                unsigned m = __ballot_sync(0xffffffffu, c);
+                while (m) {
+                    rescore_slab(s0 + __ffs(m) - 1);
+                    m &= m - 1;
                 }
             }
         }
-        if (lane == 0) {
-            if (eb > bound + step + dl) {  // nobody outside the rescored rows can reach the winner (bound -inf: no others)
-                if (ib == r_) idx1[(size_t)p * n_max + j_] = r_;
-            } else {
-                const int pos = atomicAdd(out.counters + 3, 1);
-                list1[pos] = (1u << 31) | (uint32_t)((size_t)p * n_max + j_);
-            }
-        }
+        if (lane == 0 && ib == r_) idx1[(size_t)p * n_max + j_] = r_;
     }
 }
 
@@ -919,7 +937,6 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
     if (st != FS_OK) return st;
     uint4* colkeys = keys + n;       // direction 1's key slots
     int32_t* idx1 = out.idx + n;     // arg-max row of every column (-1: no row has this column as its best)
-    uint32_t* list1 = out.list + n;  // columns that need the exact scan
     if (sp) FS_CUDA(cudaMemsetAsync(idx1, 0xFF, n * sizeof(int32_t), stream));
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
@@ -945,12 +962,9 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
         for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
             const int np = min(32768, n_pairs - p0);
             k_float_colcheck<<<dim3((n_max + 255) / 256, np), 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, p0,
-                                                                                colkeys, rowkey, out, idx1, list1);
+                                                                                colkeys, rowkey, colraw, out, idx1);
             FS_LAUNCH_CHECK("k_float_colcheck");
         }
-        k_float_fullscan<<<fs::sm_count() * 4, FSCAN_WARPS * 32, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs,
-                                                                             out, list1, out.counters + 3);
-        FS_LAUNCH_CHECK("k_float_fullscan(columns)");
     }
     if (diag) FS_CUDA(cudaMemcpyAsync(diag, out.counters, 4 * sizeof(int32_t), cudaMemcpyDeviceToDevice, stream));
     fs::FloatRowTop2 d0{out.best, out.second, out.idx};
