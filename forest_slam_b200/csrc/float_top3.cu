@@ -115,16 +115,21 @@ struct T3Epi {
     // ks: the largest chunk runner-up.  Every column other than those of k1, k2, k3 scores <= max(k3, ks).
     uint32_t k1, k2, k3, ks;
     // single-pass column side: staging addresses (bytes, shared window) and the slab's output row
-    uint32_t st_base, st_wr[4], st_rd[4], rowmask;
+    uint32_t st_base, st_wr[4], st_rd[4], rowmask, rowbits;
     bool warp_partial;
     uint32_t* col_out;
 };
 
 // one chunk of 32 columns of one row (r: its 32 accumulator values).  MASK: columns >= n1 may exist in this chunk, or
 // (single pass) rows >= n0 in this warp's 32-row group.  c: chunk counter (selects the staging tile when there are two).
-template <bool SP, bool MASK>
+// MODE: 0 = rows only (two-direction form), 1 = single pass, float scores (column side = top 16 bits of the keys),
+// 2 = single pass, Hamming (+-1 operands: the accumulator is the exact integer dot = 256 - 2 distance; the column side's
+// 16-bit value is (129 + dot / 2) << 4 | 15 - row-in-slab, so the slab maximum IS the slab's best row, lowest row first
+// on equal distance, and no certification is needed).
+template <int MODE, bool MASK>
 __device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int c, int n1, float sc, uint32_t key_mul,
                                          T3Epi& es) {
+    constexpr bool SP = MODE != 0;
     // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is shifted to the
     // global column afterwards
     const int nvalid = n1 - col0;
@@ -141,8 +146,24 @@ __device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int 
     if constexpr (SP) {
         // top 16 bits of the keys (= top 16 of the 20 live score bits), two columns per register
         uint32_t pk[16];
+        if constexpr (MODE == 2) {
+            // 2^23 + 129 + dot / 2: the low mantissa bits are the integer 129 + dot / 2 in [1, 257]; * 16 + row bits on the
+            // FMA pipe (key_mul >> 8 = 16 is a run-time value, so the multiply-add stays an IMAD)
+            const uint32_t mul16 = key_mul >> 8;
 #pragma unroll
-        for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
+            for (int j = 0; j < 16; j++) {
+                uint32_t t0 = __float_as_uint(fmaf(__uint_as_float(r[2 * j]), 0.5f, 8388737.f)) * mul16 + es.rowbits;
+                uint32_t t1 = __float_as_uint(fmaf(__uint_as_float(r[2 * j + 1]), 0.5f, 8388737.f)) * mul16 + es.rowbits;
+                if (MASK) {
+                    t0 = (2 * j < nvalid) ? t0 : 0u;
+                    t1 = (2 * j + 1 < nvalid) ? t1 : 0u;
+                }
+                pk[j] = __byte_perm(t0, t1, 0x5410);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < 16; j++) pk[j] = __byte_perm(e[2 * j], e[2 * j + 1], 0x7632);
+        }
         if (MASK) {  // rows >= n0 of the last, partially valid 32-row group
 #pragma unroll
             for (int j = 0; j < 16; j++) pk[j] &= es.rowmask;
@@ -202,13 +223,15 @@ __device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int 
 // column into (three largest slab maxima with slab ids, largest slab runner-up), and k_float_colcheck decides for every
 // row whether it is the arg-max of its best column — from those keys alone when the gaps prove it, by exact rescoring of
 // at most two slabs (32 rows) when they do not, and by an exact column scan otherwise.
-template <bool SP>
+template <int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(T3_THREADS, 1)
 k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap_half,
                 const void* __restrict__ operands, int n_max, const int32_t* __restrict__ counts,
                 const int32_t* __restrict__ pair_a, const int32_t* __restrict__ pair_b, int n_pairs_total, int pair0,
                 uint32_t key_mul, int probe, long long* __restrict__ trace, uint4* __restrict__ keys,
-                uint32_t* __restrict__ colraw) {
+                uint32_t* __restrict__ colraw, int cpitch, int nslab) {
+    // colraw [pair][nslab][cpitch]: cpitch = n_max rounded up to the 128-column tile, nslab = 2 per 32-row group
+    constexpr bool SP = MODE != 0;
 #define T3_TRACE(slot)                                                                   \
     do {                                                                                 \
         if (trace && blockIdx.x == 0 && blockIdx.z == 0 && (int)blockIdx.y == (probe >> 8)) \
@@ -354,6 +377,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             es.k1 = es.k2 = es.k3 = es.ks = 0;
             es.st_base = 0;
             es.rowmask = 0xFFFFFFFFu;
+            es.rowbits = 0;
             es.warp_partial = false;
             es.col_out = nullptr;
             if constexpr (SP) {
@@ -367,15 +391,24 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     es.st_rd[x] = par * 64 + ((((cp >> 2) ^ x) << 4) | ((cp & 3) << 2));
                 }
                 es.rowmask = (row < n0) ? 0xFFFFFFFFu : 0u;
+                es.rowbits = 15u - (uint32_t)(lane >> 1);
                 es.warp_partial = (m0 + half * 128 + quarter * 32 + 31 >= n0);
                 const int slab = ((m0 + half * 128 + quarter * 32) >> 5) * 2 + par;
-                es.col_out = colraw + ((size_t)p * (n_max >> 4) + slab) * n_max + 2 * cp;
+                es.col_out = colraw + ((size_t)p * nslab + slab) * cpitch + 2 * cp;
             }
+            // a warp whose 32 rows all lie beyond n0 only keeps the accumulator hand-shake going
+            const bool warp_dead = m0 + half * 128 + quarter * 32 >= n0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
                 tc_fence_after();
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(70 + t);
+                if (warp_dead) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                    continue;
+                }
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN + csp * T3_CW;
                 // the ragged last tile (n1 not a multiple of 128) and the last, partially valid row group run a second copy
                 // of the chunk code with the column (and, single pass, row) masks; the hot copy has none (if-converted
@@ -399,8 +432,8 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     }
 #pragma unroll
                     for (int c = 0; c < T3_CW / 32; c++) {
-                        if (masked) t3_chunk<SP, true>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
-                        else t3_chunk<SP, false>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        if (masked) t3_chunk<MODE, true>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        else t3_chunk<MODE, false>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
                     }
                 } else {
                     // chunk by chunk (the register budget of 18 warps): the buffer goes back after the last chunk's load
@@ -419,8 +452,8 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                             es.k1 = max(es.k1, rr[0] ^ rr[31]);
                             continue;
                         }
-                        if (masked) t3_chunk<SP, true>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
-                        else t3_chunk<SP, false>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        if (masked) t3_chunk<MODE, true>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        else t3_chunk<MODE, false>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
                     }
                 }
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
@@ -567,6 +600,10 @@ k_float_resolve(const void* __restrict__ operands, int n_max, const int32_t* __r
 }
 
 // ------------------------------------------------------------------------------------------------ single pass: columns
+// colraw layout (single pass): [pair][nslab][cpitch] u32
+__host__ __device__ inline int sp_cpitch(int n_max) { return (n_max + T3_BN - 1) / T3_BN * T3_BN; }
+__host__ __device__ inline int sp_nslab(int n_max) { return (n_max + 31) / 32 * 2; }
+
 // 16-bit column value (top 16 of the 20 live score bits) -> lower edge of the score interval [v, v + step)
 __device__ __forceinline__ float dec16(uint32_t v16, const fs::PairScale& ps) {
     if (v16 == 0u) return -INFINITY;
@@ -584,12 +621,13 @@ k_float_colmerge(int n_max, const int32_t* __restrict__ counts, const int32_t* _
     const int n0 = min(counts[pair_a[p]], n_max), n1 = min(counts[pair_b[p]], n_max);
     if (j >= n1) return;
     const int nsl = ((n0 + 31) >> 5) * 2;
-    const uint32_t* src = colraw + (size_t)p * (n_max >> 4) * n_max + j;
+    const int cpitch = sp_cpitch(n_max);
+    const uint32_t* src = colraw + (size_t)p * sp_nslab(n_max) * cpitch + j;
     uint32_t k1 = 0, k2 = 0, k3 = 0, ks = 0;
     for (int s0 = 0; s0 < nsl; s0 += CM_UNROLL) {
         uint32_t x[CM_UNROLL];
 #pragma unroll
-        for (int u = 0; u < CM_UNROLL; u++) x[u] = (s0 + u < nsl) ? __ldg(src + (size_t)(s0 + u) * n_max) : 0u;
+        for (int u = 0; u < CM_UNROLL; u++) x[u] = (s0 + u < nsl) ? __ldg(src + (size_t)(s0 + u) * cpitch) : 0u;
 #pragma unroll
         for (int u = 0; u < CM_UNROLL; u++) {
             const uint32_t h = x[u] & 0xFFFFu;
@@ -692,10 +730,11 @@ k_float_colcheck(const void* __restrict__ operands, int n_max, const int32_t* __
         if (!(eb > bound + step + dl)) {  // (warp-uniform: eb is the same in every lane)
             if (lane == 0) atomicAdd(out.counters + 3, 1);
             const int nsl = ((n0 + 31) >> 5) * 2;
-            const uint32_t* src = colraw + (size_t)p * (n_max >> 4) * n_max + j_;
+            const int cpitch = sp_cpitch(n_max);
+            const uint32_t* src = colraw + (size_t)p * sp_nslab(n_max) * cpitch + j_;
             for (int s0 = 0; s0 < nsl; s0 += 32) {
                 const int sl = s0 + lane;
-                const uint32_t h = (sl < nsl) ? (__ldg(src + (size_t)sl * n_max) & 0xFFFFu) : 0u;
+                const uint32_t h = (sl < nsl) ? (__ldg(src + (size_t)sl * cpitch) & 0xFFFFu) : 0u;
                 const bool c = sl < nsl && sl != a1 && sl != a2 && h != 0u && (dec16(h, ps) + step + dl > eb);
                 unsigned m = __ballot_sync(0xffffffffu, c);
                 while (m) {
@@ -788,7 +827,7 @@ k_float_slabscan(const void* __restrict__ operands, int n_max, const int32_t* __
         const __half* bank_a = static_cast<const __half*>(operands) + (size_t)fa * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
         const __half* bank_b = static_cast<const __half*>(operands) + (size_t)fb * fs::op_rows(n_max) * fs::OP_ROW_HALFS;
         const fs::OpRow8 a = fs::load_op_row(bank_a + (size_t)row * fs::OP_ROW_HALFS, lane);
-        const uint32_t* src = colraw + ((size_t)p * (n_max >> 4) + ((row >> 5) * 2 + (row & 1))) * n_max;
+        const uint32_t* src = colraw + ((size_t)p * sp_nslab(n_max) + ((row >> 5) * 2 + (row & 1))) * sp_cpitch(n_max);
         fs::Top2 t;
         t.init();
         for (int j0 = 0; j0 < n1; j0 += 128) {
@@ -839,28 +878,37 @@ extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {
     // keys (16 B) + best, second, idx, list (4 B each) for both directions + counters
     size_t bytes = fs::align_up(n2 * 16, 256) + 4 * fs::align_up(n2 * 4, 256) + 256 + 256;
     // single-pass form: row keys of the chosen columns + slab results [pair][n_max / 16 slabs][n_max] (4 B each)
-    bytes += fs::align_up(n * 4, 256) + fs::align_up((size_t)n_pairs * ((n_max + 15) / 16) * n_max * 4, 256);
+    bytes += fs::align_up(n * 4, 256) + fs::align_up(fs::float_top3_colraw_elems(n_pairs, n_max) * 4, 256);
     return bytes;
 }
 
 // the tensor-core pass alone: top-3 keys of every row of both directions (also the first stage of the tensor-core
 // Hamming matcher, hamming_tc.cu: +-1 operands make the same kernel an exact integer scorer)
+size_t fs::float_top3_colraw_elems(int n_pairs, int n_max) {
+    return (size_t)n_pairs * sp_nslab(n_max) * sp_cpitch(n_max);
+}
+
 int fs::launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
                           const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
-                          int probe, long long* trace, uint32_t* colraw) {
-    static int granted[64], granted_sp[64];
-    const int st_ = colraw ? fs::ensure_dyn_smem(k_float_top3_tc<true>, granted_sp, (size_t)(T3_SP_SMEM_BYTES))
-                           : fs::ensure_dyn_smem(k_float_top3_tc<false>, granted, (size_t)(T3_SMEM_BYTES));
+                          int probe, long long* trace, uint32_t* colraw, bool hamming) {
+    static int granted[64], granted_sp[64], granted_hm[64];
+    const int cpitch = sp_cpitch(n_max), nslab = sp_nslab(n_max);
+    const int st_ = !colraw ? fs::ensure_dyn_smem(k_float_top3_tc<0>, granted, (size_t)(T3_SMEM_BYTES))
+                    : hamming ? fs::ensure_dyn_smem(k_float_top3_tc<2>, granted_hm, (size_t)(T3_SP_SMEM_BYTES))
+                              : fs::ensure_dyn_smem(k_float_top3_tc<1>, granted_sp, (size_t)(T3_SP_SMEM_BYTES));
     if (st_ != FS_OK) return st_;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
         dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, colraw ? 1 : 2);  // clusters of two along x
-        if (colraw)
-            k_float_top3_tc<true><<<grid, T3_THREADS, T3_SP_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a,
-                                                                                  pair_b, n_pairs, p0, 4096u, probe, trace, keys, colraw);
+        if (colraw && hamming)
+            k_float_top3_tc<2><<<grid, T3_THREADS, T3_SP_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b,
+                                                                               n_pairs, p0, 4096u, probe, trace, keys, colraw, cpitch, nslab);
+        else if (colraw)
+            k_float_top3_tc<1><<<grid, T3_THREADS, T3_SP_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b,
+                                                                               n_pairs, p0, 4096u, probe, trace, keys, colraw, cpitch, nslab);
         else
-            k_float_top3_tc<false><<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a,
-                                                                                pair_b, n_pairs, p0, 4096u, probe, trace, keys, nullptr);
+            k_float_top3_tc<0><<<grid, T3_THREADS, T3_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b,
+                                                                            n_pairs, p0, 4096u, probe, trace, keys, nullptr, 0, 0);
         FS_LAUNCH_CHECK("k_float_top3_tc");
     }
     return FS_OK;
@@ -886,7 +934,7 @@ extern "C" int fs_float_top3_keys(const void* operands, int n_frames, int n_max,
     for (int i = 0; i < 4; i++) ws.take<float>(n2);
     ws.take<int32_t>(64);
     ws.take<uint32_t>(n);
-    uint32_t* colraw = ws.take<uint32_t>((size_t)n_pairs * (n_max / 16) * n_max);
+    uint32_t* colraw = ws.take<uint32_t>(fs::float_top3_colraw_elems(n_pairs, n_max));
     // probe bit 2: the two-direction kernel even where fs_float_match would run the single-pass form
     const bool sp = single_pass_enabled() && n_max % 128 == 0 && !(probe & 4);
     return fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys,
@@ -928,7 +976,7 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
     out.list = ws.take<uint32_t>(n2);
     out.counters = ws.take<int32_t>(64);
     uint32_t* rowkey = ws.take<uint32_t>(n);
-    uint32_t* colraw = ws.take<uint32_t>((size_t)n_pairs * (n_max / 16) * n_max);
+    uint32_t* colraw = ws.take<uint32_t>(fs::float_top3_colraw_elems(n_pairs, n_max));
     // single pass: direction 0 on the tensor cores, the column side from the slab keys (see k_float_top3_tc<true>)
     const bool sp = cross_check && single_pass_enabled() && n_max % 128 == 0;
     FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));

@@ -16,6 +16,7 @@
 //                         lo = 0, statistics row = |row|^2 = 256), once per FRAME;
 //   fs_hamming_match_tc : k_float_top3_tc (both directions) + k_hamming_tc_finalize (decode, crossCheck, ratio, -1 fill).
 #include <cuda.h>
+#include <stdlib.h>
 #include <cuda_fp16.h>
 #include "float_ops.cuh"
 
@@ -103,6 +104,44 @@ k_hamming_tc_finalize(const void* __restrict__ operands, int n_max, const int32_
     }
 }
 
+// Single-pass form: thread = (pair, train row t).  The slab results of column t hold, per slab of 16 query rows,
+// (129 + dot / 2) << 4 | 15 - m  of the slab's best row (row = 32 * (slab >> 1) + 2 m + (slab & 1)); the largest
+// (value, lowest row) over the slabs is the train row's best query exactly as the reverse pass would report it.
+// Written in the key format of direction 1 (only the column field is read by the finalize kernel).
+__global__ void __launch_bounds__(256)
+k_hamming_colmerge(int n_max, const int32_t* __restrict__ counts, const int32_t* __restrict__ pair_a,
+                   const int32_t* __restrict__ pair_b, const uint32_t* __restrict__ colraw, int cpitch, int nslab,
+                   uint4* __restrict__ keys1) {
+    const int p = blockIdx.y, t = blockIdx.x * 256 + threadIdx.x;
+    const int n0 = min(counts[pair_a[p]], n_max), n1 = min(counts[pair_b[p]], n_max);
+    if (t >= n1) return;
+    const int nsl = ((n0 + 31) >> 5) * 2;
+    const uint32_t* src = colraw + (size_t)p * nslab * cpitch + t;
+    uint32_t best = 0;
+    for (int s0 = 0; s0 < nsl; s0 += 8) {
+        uint32_t x[8];
+#pragma unroll
+        for (int u = 0; u < 8; u++) x[u] = (s0 + u < nsl) ? __ldg(src + (size_t)(s0 + u) * cpitch) : 0u;
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            const uint32_t h = x[u] & 0xFFFFu;
+            const int sl = s0 + u;
+            const int row = (sl >> 1) * 32 + 2 * (15 - (int)(h & 15u)) + (sl & 1);
+            best = max(best, h ? (((h >> 4) << 12) | (uint32_t)(4095 - row)) : 0u);
+        }
+    }
+    keys1[(size_t)p * n_max + t] = make_uint4(best, 0u, 0u, 0u);
+}
+
+// FS_TUNE_HAMMING_SINGLE_PASS=0 keeps fs_hamming_match_tc on the two-direction kernel (A/B measurements)
+bool hamming_single_pass_enabled() {
+    static const bool on = [] {
+        const char* e = getenv("FS_TUNE_HAMMING_SINGLE_PASS");
+        return !(e && e[0] == '0');
+    }();
+    return on;
+}
+
 }  // namespace
 
 extern "C" size_t fs_hamming_operand_bytes(int n_frames, int n_max) { return fs_float_operand_bytes(n_frames, n_max); }
@@ -123,7 +162,9 @@ extern "C" int fs_hamming_prepare(const uint8_t* desc, int n_frames, int n_max, 
 
 extern "C" size_t fs_hamming_match_tc_workspace_bytes(int n_pairs, int n_max) {
     if (n_pairs <= 0 || n_max <= 0) return 256;
-    return fs::align_up(2 * (size_t)n_pairs * n_max * sizeof(uint4), 256) + 256;
+    // keys of both directions + (single-pass form) the slab results of the column side
+    return fs::align_up(2 * (size_t)n_pairs * n_max * sizeof(uint4), 256) +
+           fs::align_up(fs::float_top3_colraw_elems(n_pairs, n_max) * 4, 256) + 256;
 }
 
 extern "C" int fs_hamming_match_tc(const void* operands, int n_frames, int n_max, const int32_t* counts,
@@ -155,8 +196,23 @@ extern "C" int fs_hamming_match_tc(const void* operands, int n_frames, int n_max
     uint4* keys = ws.take<uint4>(2 * n);
     if (matches1) FS_CUDA(cudaMemsetAsync(matches1, 0xFF, n * sizeof(int32_t), stream));
     if (n_matches) FS_CUDA(cudaMemsetAsync(n_matches, 0, (size_t)n_pairs * sizeof(int32_t), stream));
-    st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream);
+    // crossCheck: single pass (direction 0 on the tensor cores, the train rows' best queries from the slab results);
+    // without it only direction 0 is needed at all
+    uint32_t* colraw = ws.take<uint32_t>(fs::float_top3_colraw_elems(n_pairs, n_max));
+    const bool sp = cross_check && hamming_single_pass_enabled();
+    st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream, 0, nullptr,
+                               sp ? colraw : nullptr, true);
     if (st != FS_OK) return st;
+    if (sp) {
+        const int cpitch = (n_max + 127) / 128 * 128, nslab = (n_max + 31) / 32 * 2;
+        for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
+            const int np = min(32768, n_pairs - p0);
+            k_hamming_colmerge<<<dim3((n_max + 255) / 256, np), 256, 0, stream>>>(
+                n_max, counts, pair_a + p0, pair_b + p0, colraw + (size_t)p0 * nslab * cpitch, cpitch, nslab,
+                keys + n + (size_t)p0 * n_max);
+            FS_LAUNCH_CHECK("k_hamming_colmerge");
+        }
+    }
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
         const size_t o = (size_t)p0 * n_max;

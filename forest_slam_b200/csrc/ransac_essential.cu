@@ -46,6 +46,7 @@ __device__ __forceinline__ void stage_points(const float* mk0, const float* mk1,
 // ------------------------------------------------------------------------------------------------ engine policy
 struct EPolicy {
     static constexpr int FIRST_CHUNK = 48;         // speculative iterations per pair in round 0 (~30 are typical; profiles/r01zv)
+    static constexpr int FIRST_CHUNK_MIN = 32;     // ... large batches go down to this (ransac_grid.cuh: make_plan)
     static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
     static constexpr int SOLVE_WARPS_PER_SM_MAX = 6;  // ... when round 0 has more solves than 4 warps per SM have lanes
     static constexpr const char* TUNE_FIRST = "FS_TUNE_E_FIRST_CHUNK";

@@ -80,7 +80,17 @@ template <class Pol>
 inline Plan make_plan(int n_pairs, int max_iters) {
     Plan pl;
     const int mi = max_iters < 1 ? 1 : max_iters;
-    const int FIRST_CHUNK = min(256, max(Pol::SLAB, tune(Pol::TUNE_FIRST, Pol::FIRST_CHUNK) / Pol::SLAB * Pol::SLAB));
+    int first = tune(Pol::TUNE_FIRST, 0);
+    if (first <= 0) {
+        // Round 0 runs one solve per thread, and its latency is that of the fullest scheduler: up to ~4.4 solver warps
+        // per SM the sub-partitions hold one warp each (a few hold two), beyond that every solve slows down.  Large
+        // batches therefore speculate a little less per pair (measured, mono 512 pairs per step: first chunk 24 / 32 /
+        // 40 / 48 / 56 -> 95k / 102k / 106k / 100k / 89k pairs/s); the pairs that need more get them in round 1.
+        first = Pol::FIRST_CHUNK;
+        const long long lanes = (long long)(4.4 * 32 * fs::sm_count());
+        while (first > Pol::FIRST_CHUNK_MIN && (long long)n_pairs * first > lanes) first -= Pol::SLAB;
+    }
+    const int FIRST_CHUNK = min(256, max(Pol::SLAB, first / Pol::SLAB * Pol::SLAB));
     pl.first_chunk = FIRST_CHUNK;
     pl.solve_warps_per_sm = tune(Pol::TUNE_WARPS, Pol::SOLVE_WARPS_PER_SM);
     int spp = 256;

@@ -90,6 +90,7 @@ k_score_pnp(const float* __restrict__ points3d, const float* __restrict__ pts2d,
 //   finish : mask of the winner (identical arithmetic) + ascending inlier index list.
 struct PPolicy {
     static constexpr int FIRST_CHUNK = 192;        // speculative iterations per pair in round 0 (~390 are typical)
+    static constexpr int FIRST_CHUNK_MIN = 192;    // (no batch-size dependence: the sweep is flat, profiles/README.md)
     static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
     static constexpr int SOLVE_WARPS_PER_SM_MAX = 4;  // two CTAs of 64 fill the SM's shared memory (78 KB each)
     static constexpr const char* TUNE_FIRST = "FS_TUNE_P_FIRST_CHUNK";
