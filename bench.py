@@ -801,7 +801,7 @@ def run_float4096(args, ctx: Ctx):
             "scaling": "weak", "config": {"workload": "float 256-d descriptor mutual-NN + ratio test (0.8), whole "
                                           "fs_float_match call (top-3 pass + certification + finalize)",
                                           "kpts_per_frame": n, "pairs_per_launch": P},
-            "roofline": {"kernel": "fs_float_match (k_float_top3_tc + resolve + fullscan + finalize)", "bound": "tensor",
+            "roofline": {"kernel": "fs_float_match (single-pass k_float_top3_tc + colmerge + resolve + slabscan + colcheck + finalize)", "bound": "tensor",
                          "achieved": f["tflops"], "peak": ctx.peaks["bf16_tflops"], "unit": "TFLOP/s",
                          "frac": f["frac_of_bf16_burst"], "peak_source": ctx.peaks["source"]},
             "cases": out}

@@ -160,7 +160,7 @@ def main():
                  {"flop": flop, "popc32_equivalent": popc, "equiv_gpopc32_per_s": popc / ms_t / 1e6,
                   "speedup_vs_popc_kernel": ms / ms_t, "prepare_ms_per_%d_frames" % F: ms_p},
                  "tensor", flop / ms_t / 1e9, pk["tensor_tflops"], "TFLOP/s",
-                 "one fp16 tcgen05 pass per direction (2x the algorithmic MMA work, roofline counts 1x); exact integers")
+                 "single fp16 tcgen05 pass (crossCheck from the slab maxima of the column side); exact integers")
 
     # ------------------------------------------------------------------ config 5: all-pairs loop-closure matching
     if on("loopclosure"):
@@ -217,7 +217,7 @@ def main():
             b = a + 1
             ms = T(lambda: fsb.float_match_batch(None, counts, a, b, operands=ops))
             fl = pp * 2.0 * n * n * 256
-            line("fs_float_match (top3_tc + resolve + fullscan + finalize)", {"pairs": pp, "n": n,
+            line("fs_float_match (single-pass top3_tc + colmerge + resolve + slabscan + colcheck + finalize)", {"pairs": pp, "n": n,
                  "descriptors": "random unit vectors (worst case for certification: no inlier margin)"}, ms,
                  {"flop": fl}, "tensor", fl / ms / 1e9, pk["tensor_tflops"], "TFLOP/s")
             ms3 = T(lambda: fsb.float_match_batch(None, counts, a, b, operands=ops, split3=True))
