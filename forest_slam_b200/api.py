@@ -31,7 +31,7 @@ NORM_L2 = 4       # cv2.NORM_L2
 RANSAC = 8        # cv2.RANSAC
 SOLVEPNP_ITERATIVE = 0
 
-# the tcgen05 matchers are the default: csrc/float_top3.cu (certified single fp16 pass per direction; also the Hamming
+# the tcgen05 matchers are the default: csrc/float_top3.cu (certified single fp16 pass per frame pair; also the Hamming
 # path on +-1 operands, csrc/hamming_tc.cu); csrc/float_tc.cu (three-MMA split-fp16) on request or above 4096 columns;
 # the exact-fp32 CUDA-core kernel serves descriptor counts that are not a multiple of 128 and `exact_fp32=True`
 TENSOR_CORE_MATCHER = True

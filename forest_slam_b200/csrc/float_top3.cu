@@ -1,32 +1,33 @@
-// float_top3.cu — A1 (float descriptor mutual-NN, superglue.py:259-260, :268-278) as ONE fp16 tensor-core pass per
-// direction with certified results.
+// float_top3.cu — A1 (float descriptor mutual-NN, superglue.py:259-260, :268-278) as ONE fp16 tensor-core pass per frame
+// pair with certified results.
 //
 // Why: the split-fp16 kernel (float_tc.cu) needs three MMAs per k-step to be fp32-grade and a cross-lane column
 // reduction in its epilogue; both cap it at ~20 % of the algorithmic tensor roofline.  Here the contraction runs ONCE
-// on the hi halves (fp16 x fp16 -> fp32 in TMEM), once per direction (rows of a against b, rows of b against a: the
-// column side of superglue.py:268 becomes a row problem, so the epilogue never leaves the thread), and the epilogue
-// keeps each row's TOP-3 packed keys.  A rigorous bound delta on |exact - tensor-core score| (float_ops.cuh) then
-// decides, row by row, what the approximate keys already prove:
-//   best - second  > 2 delta : the arg-max is certain;
-//   best - third   > 2 delta : the arg-max is one of two columns -> both are rescored exactly (fp32, hi + lo);
-//   otherwise                : the row is rescanned exactly over all columns (rare: k_float_fullscan).
+// on the hi halves (fp16 x fp16 -> fp32 in TMEM) and the epilogue keeps, per row, the TOP-3 packed keys, and per column
+// (single-pass form, k_float_top3_tc<1>) the best / runner-up 16-bit value of every slab of 16 rows.  A rigorous bound
+// delta on |exact - tensor-core score| (float_ops.cuh) then decides what the approximate keys already prove:
+//   rows   : best - second > 2 delta: the arg-max is certain; best - third > 2 delta: it is one of two columns -> both
+//            are rescored exactly (fp32, hi + lo); otherwise the row is listed and rescored from the slab bound
+//            (k_float_slabscan), or, in the two-direction form, rescanned over all columns (k_float_fullscan);
+//   columns: is the row the arg-max of its best column?  k_float_colmerge / k_float_colcheck (see there).
 // The same interval test guards the threshold and the ratio decisions.  Index sets are therefore those of the exact
 // score, never of the fp16 one; score values are exact where a decision depended on them and within delta elsewhere.
 //
-// Why two directions and not one pass with a column reduction: measured on B200 (256 pairs x 2048^2, this kernel's grid).
-// The two-direction form is bound by the tensor pipe (MMAs only: 0.77 ms, 105 clk per 128x128x16 = 89 % of what cuBLAS
-// sustains; epilogue only: 0.65 ms; together 0.955 ms).  A single-pass variant that also reduced every column over the
-// CTA's 256 rows (redux.sync twice per score for best + runner-up, warps merged in shared memory, row blocks in the
-// resolver) halved the MMA work but its epilogue alone took 0.93 ms (CREDUX + uniform->vector moves; a shuffle butterfly
-// needs ~5.3 ALU ops per score against 2.6 here): 1.01 ms in total, so it was dropped.
+// History (measured on B200, 256 pairs x 2048^2).  The two-direction form (k_float_top3_tc<0>: rows of a against b, then
+// rows of b against a, so that the column side is a row problem and the epilogue never leaves the thread) was bound by
+// the tensor pipe doing twice the algorithmic work: 0.955 ms.  A first single-pass attempt that reduced the columns with
+// redux.sync was slower (1.01 ms: CREDUX + uniform->vector moves; a 32-bit shuffle butterfly needs ~5.3 ALU operations
+// per score).  What works is 16-bit packing: the top 16 of the 20 live key bits, two columns per register, transposed
+// through a per-warp shared-memory tile and reduced with VIMNMX.U16x2 (1.2 ALU operations per score): 0.527 ms.
 //
-// k_float_top3_tc — one CTA = (direction, frame pair, 256-row block of the "row" frame), 320 threads:
-//   warp 8    : TMA producer.  The row block (2 x 128 rows x 256 fp16 = 128 KB) is loaded once and stays resident;
+// k_float_top3_tc — one CTA = ([direction,] frame pair, 256-row block of the "row" frame), 18 warps:
+//   warp 16   : TMA producer.  The row block (2 x 128 rows x 256 fp16 = 128 KB) is loaded once and stays resident;
 //               the other frame streams through a 4-stage ring of [128 x 64] boxes (16 KB, 128-byte swizzle);
-//   warp 9    : MMA issuer: per 128-column tile 2 x 16 tcgen05.mma (128x128x16, kind::f16) into two of four TMEM
+//   warp 17   : MMA issuer: per 128-column tile 2 x 16 tcgen05.mma (128x128x16, kind::f16) into two of four TMEM
 //               accumulators (2 row halves x double buffer = 512 columns); tcgen05.commit frees ring stages / publishes;
-//   warps 0-7 : epilogue, thread = row: tcgen05.ld 32x32b, key = bits(fma(v, sc, bias)) * 4096 + (4095 - col)  (FMA
-//               pipe), top-3 by a min/max merge network on the keys (ALU pipe, 4 ops per element).
+//   warps 0-15: epilogue, thread = row, 32 columns at a time: tcgen05.ld 32x32b, key = bits(fma(v, sc, bias)) * 4096 +
+//               (4095 - col) (FMA pipe), tournament top-2 of the chunk + top-3 of the chunk maxima (ALU pipe); single
+//               pass: pack, staging tile, transposed read-back, packed tournament, slab results to global memory.
 #include <cuda.h>
 #include <cuda_fp16.h>
 #include "float_ops.cuh"

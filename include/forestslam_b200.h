@@ -109,10 +109,11 @@ int fs_hamming_match_tc(const void* operands_fp16, int n_frames, int n_max, cons
  *
  * Two-step: fs_float_prepare() turns a frame bank of channel-major fp32 descriptors (SuperPoint layout
  * [256, n], superpoint.py:90-91) into the K-major split-fp16 operand bank the tensor-core kernels read
- * (once per FRAME, not per pair); fs_float_match() then runs ONE fp16 tcgen05 pass per direction with a
- * fused row top-3 epilogue, certifies every arg-max / threshold / ratio decision against a rigorous
- * error bound (rescoring exactly, in fp32 on hi + lo, whatever the fp16 pass cannot prove) and applies
- * the mutual / threshold / ratio finalisation.  Index outputs are those of the exact score.
+ * (once per FRAME, not per pair); fs_float_match() then runs ONE fp16 tcgen05 pass per frame pair with a
+ * fused epilogue (row top-3 keys; column side of the mutual check as packed 16-bit maxima per slab of 16
+ * rows), certifies every arg-max / mutual / threshold / ratio decision against a rigorous error bound
+ * (rescoring exactly, in fp32 on hi + lo, whatever the fp16 pass cannot prove) and applies the mutual /
+ * threshold / ratio finalisation.  Index outputs are those of the exact score.
  *
  * desc_f32   [n_frames, 256, n_max] f32   channel-major
  * operands   [n_frames, n_max + 1, 512] fp16: rows < n_max = (hi | lo) split, x = hi + lo to 2^-25, rows
@@ -124,7 +125,8 @@ int fs_hamming_match_tc(const void* operands_fp16, int n_frames, int n_max, cons
  *   -inf when none), matches1 i32; n_matches [n_pairs].  score0/second0/matches1/n_matches may be NULL.
  *   fs_float_match: score0 / second0 are exact wherever a decision depended on them and within the
  *   bound (~3e-4 for unit descriptors) elsewhere; fs_float_match_split3 / _fp32 give fp32-grade values.
- * diag       NULL or 4 x i32 on the device: [0] rows rescanned exactly, [1] rows with rescored candidates
+ * diag       NULL or 4 x i32 on the device: [0] rows rescored from the slab bound (or rescanned), [1] rows with two
+ *            rescored candidates, [2] rows whose column check rescored slabs, [3] ... with a widened slab search
  * n_max      fs_float_match: <= 4096 (FS_ERR_UNSUPPORTED above; use fs_float_match_split3)
  * ---------------------------------------------------------------------------------------------- */
 #define FS_FLOAT_DIM 256
