@@ -105,7 +105,7 @@ int encode_operand_map(const void* operands, int n_frames, int n_max, CUtensorMa
 int launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max,
                       const int32_t* counts, const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys,
                       cudaStream_t stream, int probe = 0, long long* trace = nullptr, uint32_t* colraw = nullptr,
-                      bool hamming = false);
+                      bool hamming = false, int ndirs = 2);
 // single-pass forms (colraw != nullptr): direction 0 only, slab results of the column side into
 // colraw [n_pairs][2 * ceil(n_max / 32)][n_max rounded up to 128] u32 (float_top3.cu); element count:
 size_t float_top3_colraw_elems(int n_pairs, int n_max);

@@ -891,7 +891,7 @@ size_t fs::float_top3_colraw_elems(int n_pairs, int n_max) {
 
 int fs::launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half, const void* operands, int n_max, const int32_t* counts,
                           const int32_t* pair_a, const int32_t* pair_b, int n_pairs, uint4* keys, cudaStream_t stream,
-                          int probe, long long* trace, uint32_t* colraw, bool hamming) {
+                          int probe, long long* trace, uint32_t* colraw, bool hamming, int ndirs) {
     static int granted[64], granted_sp[64], granted_hm[64];
     const int cpitch = sp_cpitch(n_max), nslab = sp_nslab(n_max);
     const int st_ = !colraw ? fs::ensure_dyn_smem(k_float_top3_tc<0>, granted, (size_t)(T3_SMEM_BYTES))
@@ -900,7 +900,7 @@ int fs::launch_float_top3(const CUtensorMap& tmap, const CUtensorMap& tmap_half,
     if (st_ != FS_OK) return st_;
     for (int p0 = 0; p0 < n_pairs; p0 += 32768) {
         const int np = min(32768, n_pairs - p0);
-        dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, colraw ? 1 : 2);  // clusters of two along x
+        dim3 grid(((n_max + T3_ROWS - 1) / T3_ROWS + 1) / 2 * 2, np, colraw ? 1 : ndirs);  // clusters of two along x
         if (colraw && hamming)
             k_float_top3_tc<2><<<grid, T3_THREADS, T3_SP_SMEM_BYTES, stream>>>(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b,
                                                                                n_pairs, p0, 4096u, probe, trace, keys, colraw, cpitch, nslab);
@@ -982,7 +982,7 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
     const bool sp = cross_check && single_pass_enabled() && n_max % 128 == 0;
     FS_CUDA(cudaMemsetAsync(out.counters, 0, 64 * sizeof(int32_t), stream));
     st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream, 0,
-                               nullptr, sp ? colraw : nullptr);
+                               nullptr, sp ? colraw : nullptr, false, cross_check ? 2 : 1);
     if (st != FS_OK) return st;
     uint4* colkeys = keys + n;       // direction 1's key slots
     int32_t* idx1 = out.idx + n;     // arg-max row of every column (-1: no row has this column as its best)
@@ -993,7 +993,7 @@ static int float_match_impl(const void* operands, int n_frames, int n_max, const
             k_float_colmerge<<<dim3((n_max + 255) / 256, np), 256, 0, stream>>>(n_max, counts, pair_a, pair_b, p0, colraw, colkeys);
             FS_LAUNCH_CHECK("k_float_colmerge");
         }
-        dim3 rgrid((n_max + 255) / 256, np, sp ? 1 : 2);
+        dim3 rgrid((n_max + 255) / 256, np, (sp || !cross_check) ? 1 : 2);  // knn use: direction 0 only
         k_float_resolve<<<rgrid, 256, 0, stream>>>(operands, n_max, counts, pair_a, pair_b, n_pairs, p0, keys, scale,
                                                    threshold, ratio, out, sp ? rowkey : nullptr);
         FS_LAUNCH_CHECK("k_float_resolve");

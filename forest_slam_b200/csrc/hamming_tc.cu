@@ -201,7 +201,7 @@ extern "C" int fs_hamming_match_tc(const void* operands, int n_frames, int n_max
     uint32_t* colraw = ws.take<uint32_t>(fs::float_top3_colraw_elems(n_pairs, n_max));
     const bool sp = cross_check && hamming_single_pass_enabled();
     st = fs::launch_float_top3(tmap, tmap_half, operands, n_max, counts, pair_a, pair_b, n_pairs, keys, stream, 0, nullptr,
-                               sp ? colraw : nullptr, true);
+                               sp ? colraw : nullptr, true, cross_check ? 2 : 1);
     if (st != FS_OK) return st;
     if (sp) {
         const int cpitch = (n_max + 127) / 128 * 128, nslab = (n_max + 31) / 32 * 2;
