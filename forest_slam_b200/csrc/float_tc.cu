@@ -169,36 +169,46 @@ k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int3
     tc_fence_after();
     const uint32_t tmem_base = bar.tmem_base;
 
+    // TMA and MMA warps loop converged and elect one lane per asynchronous instruction, so that addresses and descriptors
+    // stay in uniform registers (float_top3.cu has the measurement: under `if (lane == 0)` every UTCHMMA / UTMALDG sits in
+    // an ELECT / R2UR.BROADCAST / BRA.U.ANY loop of ~13 dependent instructions)
     if (warp == 0) {
-        // ===================================================== TMA producer (one thread)
-        if (lane == 0 && ntiles > 0) {
-            mbar_arrive_expect_tx(&bar.a_full, TC_A_BYTES);
-            for (int h = 0; h < 2; h++)
-                for (int kc = 0; kc < TC_KCH; kc++)
-                    tma_load_3d(sA + (h * TC_KCH + kc) * TC_TILE_BYTES, &tmap, &bar.a_full, h * 256 + kc * TC_BK, m0, fa);
+        // ===================================================== TMA producer
+        if (ntiles > 0) {
+            if (elect_one()) {
+                mbar_arrive_expect_tx(&bar.a_full, TC_A_BYTES);
+                for (int h = 0; h < 2; h++)
+                    for (int kc = 0; kc < TC_KCH; kc++)
+                        tma_load_3d(sA + (h * TC_KCH + kc) * TC_TILE_BYTES, &tmap, &bar.a_full, h * 256 + kc * TC_BK, m0, fa);
+            }
+            __syncwarp();
             int it = 0;
             for (int t = 0; t < ntiles; t++)
                 for (int kc = 0; kc < TC_KCH; kc++, it++) {
                     const int s = it % TC_STAGES;
                     mbar_wait(&bar.empty[s], ((it / TC_STAGES) & 1) ^ 1);
-                    mbar_arrive_expect_tx(&bar.full[s], TC_STAGE_BYTES);
-                    uint8_t* dst = sB + s * TC_STAGE_BYTES;
-                    tma_load_3d(dst, &tmap, &bar.full[s], kc * TC_BK, t * TC_BN, fb);
-                    tma_load_3d(dst + TC_TILE_BYTES, &tmap, &bar.full[s], 256 + kc * TC_BK, t * TC_BN, fb);
+                    if (elect_one()) {
+                        mbar_arrive_expect_tx(&bar.full[s], TC_STAGE_BYTES);
+                        uint8_t* dst = sB + s * TC_STAGE_BYTES;
+                        tma_load_3d(dst, &tmap, &bar.full[s], kc * TC_BK, t * TC_BN, fb);
+                        tma_load_3d(dst + TC_TILE_BYTES, &tmap, &bar.full[s], 256 + kc * TC_BK, t * TC_BN, fb);
+                    }
+                    __syncwarp();
                 }
         }
     } else if (warp == 1) {
-        // ===================================================== MMA issuer (one thread)
-        if (lane == 0 && ntiles > 0) {
+        // ===================================================== MMA issuer
+        if (ntiles > 0) {
             mbar_wait(&bar.a_full, 0);
             tc_fence_after();
             const uint32_t a_addr = smem_u32(sA), b_addr = smem_u32(sB);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);  // (tells the compiler it is warp-uniform)
             int it = 0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_empty[buf], ((t >> 1) & 1) ^ 1);
                 tc_fence_after();
-                const uint32_t d = tmem_base + buf * TC_BN;
+                const uint32_t d = tmem_u + buf * TC_BN;
                 for (int kc = 0; kc < TC_KCH; kc++, it++) {
                     const int s = it % TC_STAGES;
                     mbar_wait(&bar.full[s], (it / TC_STAGES) & 1);
@@ -207,16 +217,20 @@ k_float_match_tc(const __grid_constant__ CUtensorMap tmap, int n_max, const int3
                     const uint64_t a_lo = make_desc_k_sw128(a_addr + (TC_KCH + kc) * TC_TILE_BYTES);
                     const uint64_t b_hi = make_desc_k_sw128(b_addr + s * TC_STAGE_BYTES);
                     const uint64_t b_lo = make_desc_k_sw128(b_addr + s * TC_STAGE_BYTES + TC_TILE_BYTES);
+                    if (elect_one()) {
 #pragma unroll
-                    for (int ks = 0; ks < TC_BK / 16; ks++) {
-                        const uint64_t o = (uint64_t)(ks * 32 >> 4);  // +32 bytes per K = 16 step inside the swizzle row
-                        umma_f16(d, a_hi + o, b_hi + o, TC_IDESC, (kc | ks) != 0);
-                        umma_f16(d, a_lo + o, b_hi + o, TC_IDESC, 1);
-                        umma_f16(d, a_hi + o, b_lo + o, TC_IDESC, 1);
+                        for (int ks = 0; ks < TC_BK / 16; ks++) {
+                            const uint64_t o = (uint64_t)(ks * 32 >> 4);  // +32 bytes per K = 16 step inside the swizzle row
+                            umma_f16(d, a_hi + o, b_hi + o, TC_IDESC, (kc | ks) != 0);
+                            umma_f16(d, a_lo + o, b_hi + o, TC_IDESC, 1);
+                            umma_f16(d, a_hi + o, b_lo + o, TC_IDESC, 1);
+                        }
+                        umma_commit(&bar.empty[s]);  // ring stage free once these MMAs have read it
                     }
-                    umma_commit(&bar.empty[s]);  // ring stage free once these MMAs have read it
+                    __syncwarp();
                 }
-                umma_commit(&bar.tmem_full[buf]);  // accumulator complete
+                if (elect_one()) umma_commit(&bar.tmem_full[buf]);  // accumulator complete
+                __syncwarp();
             }
         }
     } else {
