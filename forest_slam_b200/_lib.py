@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libforestslam_b200.so")
+# FORESTSLAM_B200_LIB: another build of the same library (tuning experiments: scratch/build_variant.sh)
+LIB_PATH = os.environ.get("FORESTSLAM_B200_LIB") or os.path.join(_HERE, "libforestslam_b200.so")
 
 c_i32p = C.c_void_p
 c_f32p = C.c_void_p

@@ -39,7 +39,10 @@ using namespace sm100;
 
 constexpr int T3_BN = 128, T3_BK = 64, T3_KCH = FS_FLOAT_DIM / T3_BK;  // 4 k-chunks of 64
 constexpr int T3_ROWS = 256;                                          // rows per CTA (two MMA halves of 128)
-constexpr int T3_STAGES = 4;  // one tile; (6 stages with run-time stage indexing measured SLOWER: the MMA issue thread is the
+#ifndef T3_STAGES_N
+#define T3_STAGES_N 4
+#endif
+constexpr int T3_STAGES = T3_STAGES_N;  // one tile; (6 stages with run-time stage indexing measured SLOWER: the MMA issue thread is the
                               // critical path — one tile of MMAs takes as long to issue as to execute — so it gets no extra work)
 // Epilogue warps: T3_CSPLIT warps share each 32-row TMEM lane quarter of each half and split the tile's 128 columns
 // (CSPLIT = 2: 16 warps, four per scheduler: the epilogue is a chain of dependent phases (tcgen05.ld -> keys -> staging
@@ -49,22 +52,37 @@ constexpr int T3_STAGES = 4;  // one tile; (6 stages with run-time stage indexin
 #endif
 constexpr int T3_EPI_WARPS = 8 * T3_CSPLIT;
 constexpr int T3_THREADS = (T3_EPI_WARPS + 2) * 32;
+// (registers: warps are allocated in groups of four, so 18 warps cost 20: 65536 / 640 = 102 -> 96 per thread;
+// __maxnreg__(112) compiles and then fails to launch)
 constexpr int T3_TMA_WARP = T3_EPI_WARPS, T3_MMA_WARP = T3_EPI_WARPS + 1;  // warps below are the epilogue
 constexpr int T3_CW = T3_BN / T3_CSPLIT;     // columns of a tile per epilogue warp
-constexpr int T3_NBUF = T3_CSPLIT == 1 ? 2 : 1;  // staging tiles per warp (single pass)
+// CTA pair (tcgen05 cta_group::2): the two CTAs of a cluster own neighbouring 256-row blocks and stream the SAME frame, so
+// one tcgen05.mma with M = 256 serves a 128-row half of BOTH: each CTA keeps only its 64 columns of every streamed box and
+// its tensor core reads 4 KB (own rows) + 2 KB (own columns) per instruction instead of 4 + 4 KB.  The kernel is bound by
+// shared-memory bandwidth (operand reads were half of it), and the ring shrinks to 32 KB, which pays for a second staging
+// tile per epilogue warp.  Rank 0 issues every MMA; TMA loads of either CTA signal rank 0's barriers (.cta_group::2).
+#ifndef T3_2CTA
+#define T3_2CTA 1
+#endif
+constexpr int T3_B_STAGE_BYTES = T3_2CTA ? 64 * T3_BK * 2 : 128 * T3_BK * 2;  // streamed-frame bytes per ring stage per CTA
+#ifndef T3_NBUF_N
+#define T3_NBUF_N (T3_CSPLIT == 1 ? 2 : 1)  // (CTA pair, 16 warps: a second tile measured slower, 0.563 vs 0.533 ms)
+#endif
+constexpr int T3_NBUF = T3_NBUF_N;  // staging tiles per warp (single pass)
+constexpr uint32_t T3_IDESC2 = make_idesc_f16(256, T3_BN, /*F16*/ 0);
 constexpr int T3_BOX_BYTES = 128 * T3_BK * 2;               // 16 KB: one [128 x 64] fp16 box
 constexpr int T3_A_BYTES = 2 * T3_KCH * T3_BOX_BYTES;       // 128 KB
 constexpr int T3_TMEM_COLS = 512;
 constexpr uint32_t T3_IDESC = make_idesc_f16(128, T3_BN, /*F16*/ 0);
 
 struct T3Barriers {
-    uint64_t a_full;
+    uint64_t a_full;  // CTA pair: rank 0's collects both CTAs' row blocks
     uint64_t full[T3_STAGES], empty[T3_STAGES];
     uint64_t tmem_full[2], tmem_empty[2];
     uint32_t tmem_base;
     uint32_t pad;
 };
-constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_BOX_BYTES + 256 /*barriers*/;
+constexpr int T3_SMEM_BYTES = 1024 /*alignment slack*/ + T3_A_BYTES + T3_STAGES * T3_B_STAGE_BYTES + 256 /*barriers*/;
 // single-pass variant: per epilogue warp T3_NBUF staging tiles of 32 rows x 32 packed 16-bit scores (2 KB each)
 constexpr int T3_STAGE_BYTES = 32 * 64;
 constexpr int T3_SP_SMEM_BYTES = T3_SMEM_BYTES + T3_EPI_WARPS * T3_NBUF * T3_STAGE_BYTES;
@@ -127,14 +145,18 @@ struct T3Epi {
 // 2 = single pass, Hamming (+-1 operands: the accumulator is the exact integer dot = 256 - 2 distance; the column side's
 // 16-bit value is (129 + dot / 2) << 4 | 15 - row-in-slab, so the slab maximum IS the slab's best row, lowest row first
 // on equal distance, and no certification is needed).
-template <int MODE, bool MASK>
+// after_keys(): called once the accumulator values r[] are dead (the caller prefetches the next chunk into them).
+template <int MODE, bool MASK, class F>
 __device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int c, int n1, float sc, uint32_t key_mul,
-                                         T3Epi& es) {
+                                         T3Epi& es, F&& after_keys) {
     constexpr bool SP = MODE != 0;
     // keys of this chunk carry (4095 - j), a compile-time constant per register; the chunk's best key is shifted to the
     // global column afterwards
     const int nvalid = n1 - col0;
-    if (MASK && nvalid <= 0) return;  // (warp-uniform) the slab results of an empty chunk are never read
+    if (MASK && nvalid <= 0) {  // (warp-uniform) the slab results of an empty chunk are never read
+        after_keys();
+        return;
+    }
     uint32_t e[32];
 #pragma unroll
     for (int j = 0; j < 32; j++)
@@ -176,11 +198,13 @@ __device__ __forceinline__ void t3_chunk(const uint32_t (&r)[32], int col0, int 
 #pragma unroll
         for (int cc = 0; cc < 4; cc++)
             sts128(sbuf + es.st_wr[cc], pk[4 * cc], pk[4 * cc + 1], pk[4 * cc + 2], pk[4 * cc + 3]);
+        after_keys();
         __syncwarp();
         // transposed read-back; the row tournament below runs while these loads are in flight
 #pragma unroll
         for (int m = 0; m < 16; m++) x[m] = lds32(sbuf + es.st_rd[m & 3] + m * 128);
     }
+    if constexpr (!SP) after_keys();
     uint32_t cb, cs;
     chunk_top2(e, cb, cs);
     // (4095 - j) - col0 = 4095 - (col0 + j): no borrow out of the low 12 bits; an empty chunk stays 0
@@ -255,8 +279,8 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     uint8_t* sA = smem;                 // [half][kc] boxes of 16 KB
-    uint8_t* sB = smem + T3_A_BYTES;    // [stage] boxes of 16 KB
-    T3Barriers& bar = *reinterpret_cast<T3Barriers*>(sB + T3_STAGES * T3_BOX_BYTES);
+    uint8_t* sB = smem + T3_A_BYTES;    // [stage]: boxes of 16 KB, or (CTA pair) this CTA's 64 columns of them, 8 KB
+    T3Barriers& bar = *reinterpret_cast<T3Barriers*>(sB + T3_STAGES * T3_B_STAGE_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -265,20 +289,26 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
         mbar_init(&bar.a_full, 1);
         for (int s = 0; s < T3_STAGES; s++) {
             mbar_init(&bar.full[s], 1);
-            mbar_init(&bar.empty[s], 2);
+            mbar_init(&bar.empty[s], T3_2CTA ? 1 : 2);
         }
         for (int b = 0; b < 2; b++) {
             mbar_init(&bar.tmem_full[b], 1);
-            mbar_init(&bar.tmem_empty[b], 4 * T3_CSPLIT * nhalf);
+            // every epilogue warp arrives once per tile, whether it has rows or not (CTA pair: both CTAs' warps on rank 0's)
+            mbar_init(&bar.tmem_empty[b], (T3_2CTA ? 2 : 1) * T3_EPI_WARPS);
         }
         fence_barrier_init();
     }
     if (warp == T3_MMA_WARP) {
-        tmem_alloc(&bar.tmem_base, T3_TMEM_COLS);
-        tmem_relinquish();
+        if (T3_2CTA) {
+            tmem_alloc2(&bar.tmem_base, T3_TMEM_COLS);
+            tmem_relinquish2();
+        } else {
+            tmem_alloc(&bar.tmem_base, T3_TMEM_COLS);
+            tmem_relinquish();
+        }
     }
     tc_fence_before();
-    cluster_sync_all();  // both CTAs' barriers exist before either multicasts into the other
+    cluster_sync_all();  // both CTAs' barriers exist before either signals the other's
     tc_fence_after();
     const uint32_t tmem_base = bar.tmem_base;
     if (threadIdx.x == 0) T3_TRACE(1);
@@ -288,6 +318,82 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     // descriptors in uniform registers, so a tcgen05.mma is one instruction.  (Under `if (lane == 0)` every UTCHMMA /
     // UTMALDG sat in an ELECT / R2UR.BROADCAST / BRA.U.ANY loop of ~13 dependent instructions: the MMA warp took as long
     // to issue a tile as the tensor pipe took to execute it, and any competition for its issue slots slowed the pipe.)
+#if T3_2CTA
+    // rows of the peer (rank 1 sits 256 rows further down; rank 0 always has at least as many valid halves)
+    const int peer_m0 = (int)(blockIdx.x ^ 1u) * T3_ROWS;
+    const int peer_nhalf = peer_m0 >= n0 ? 0 : ((peer_m0 + 128 < n0) ? 2 : 1);
+    const int own_nhalf = ghost ? 0 : nhalf;
+    if (warp == T3_TMA_WARP) {
+        // ===================================================== TMA producer (both CTAs; completions go to rank 0)
+        if (ntiles > 0) {
+            const uint32_t lead_a_full = mapa_u32(smem_u32(&bar.a_full), 0);
+            if (elect_one()) {
+                if (rank == 0) mbar_arrive_expect_tx(&bar.a_full, (own_nhalf + peer_nhalf) * T3_KCH * T3_BOX_BYTES);
+                for (int h = 0; h < own_nhalf; h++)
+                    for (int kc = 0; kc < T3_KCH; kc++)
+                        tma_load_3d_2sm(sA + (h * T3_KCH + kc) * T3_BOX_BYTES, &tmap, lead_a_full, kc * T3_BK, m0 + h * 128, fa);
+            }
+            __syncwarp();
+            int it = 0;
+            for (int t = 0; t < ntiles; t++) {
+#pragma unroll
+                for (int kc = 0; kc < T3_KCH; kc++, it++) {
+                    const int s = it % T3_STAGES;
+                    mbar_wait(&bar.empty[s], ((it / T3_STAGES) & 1) ^ 1);
+                    if (elect_one()) {
+                        if (rank == 0) mbar_arrive_expect_tx(&bar.full[s], 2 * T3_B_STAGE_BYTES);  // own + the peer's columns
+                        tma_load_3d_2sm(sB + s * T3_B_STAGE_BYTES, &tmap_half, mapa_u32(smem_u32(&bar.full[s]), 0), kc * T3_BK,
+                                        t * T3_BN + (int)rank * 64, fb);
+                    }
+                    __syncwarp();
+                }
+                if (lane == 0 && t < 20) T3_TRACE(10 + t);
+            }
+        }
+    } else if (warp == T3_MMA_WARP) {
+        // ===================================================== MMA issuer: rank 0 only, for both CTAs.  This warp has the
+        // highest warp id of the CTA: the sub-partition's arbiter prefers it over the epilogue warps it shares issue slots
+        // with.
+        if (ntiles > 0 && rank == 0) {
+            mbar_wait(&bar.a_full, 0);
+            tc_fence_after();
+            if (lane == 0) T3_TRACE(3);
+            const uint32_t tmem_u = __shfl_sync(0xffffffffu, tmem_base, 0);  // (tells the compiler it is warp-uniform)
+            const uint64_t a_desc0 = make_desc_k_sw128(smem_u32(sA)), b_desc0 = make_desc_k_sw128(smem_u32(sB));
+            int it = 0;
+            for (int t = 0; t < ntiles; t++) {
+                const int buf = t & 1;
+                mbar_wait(&bar.tmem_empty[buf], ((t >> 1) & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t d0 = tmem_u + (buf * 2) * T3_BN;
+                if (lane == 0 && t < 20) T3_TRACE(30 + t);
+#pragma unroll
+                for (int kc = 0; kc < T3_KCH; kc++, it++) {
+                    const int s = it % T3_STAGES;
+                    mbar_wait(&bar.full[s], (it / T3_STAGES) & 1);
+                    tc_fence_after();
+                    const uint64_t bs = b_desc0 + (uint64_t)((s * T3_B_STAGE_BYTES) >> 4);
+                    if (elect_one()) {
+#pragma unroll
+                        for (int ks = 0; ks < T3_BK / 16; ks++) {
+                            // descriptor start-address field is in 16-byte units: +2 per K = 16 step inside the swizzle row
+                            const uint64_t bd = bs + (uint64_t)((ks * 32) >> 4);
+                            const uint64_t ad = a_desc0 + (uint64_t)((kc * T3_BOX_BYTES + ks * 32) >> 4);
+                            if (probe & 1) continue;
+                            umma_f16_2cta(d0, ad, bd, T3_IDESC2, (kc | ks) != 0);
+                            if (nhalf == 2)
+                                umma_f16_2cta(d0 + T3_BN, ad + (uint64_t)((T3_KCH * T3_BOX_BYTES) >> 4), bd, T3_IDESC2, (kc | ks) != 0);
+                        }
+                        umma_commit2_multicast(&bar.empty[s], (uint16_t)3);  // both CTAs' ring stages have been read
+                    }
+                    __syncwarp();
+                }
+                if (elect_one()) umma_commit2_multicast(&bar.tmem_full[buf], (uint16_t)3);  // this tile's accumulators, both CTAs
+                __syncwarp();
+                if (lane == 0 && t < 20) T3_TRACE(50 + t);
+            }
+        }
+#else
     if (warp == T3_TMA_WARP) {
         // ===================================================== TMA producer
         if (ntiles > 0) {
@@ -365,13 +471,24 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 if (lane == 0 && t < 20) T3_TRACE(50 + t);
             }
         }
+#endif
     } else {
         // ===================================================== epilogue: warps 0..7, thread = row
         const int half = (warp >> 2) & 1;
         const int quarter = warp & 3;  // the TMEM lane quarter this warp may read
         const int csp = warp >> 3;     // which T3_CW columns of every tile
-        if (half < nhalf && !ghost) {
+        {
             const int row = m0 + half * 128 + quarter * 32 + lane;
+            // hands an accumulator buffer back to the MMA issuer (CTA pair: rank 0's barrier collects both CTAs' warps)
+            const uint32_t rel_bar0 = T3_2CTA ? mapa_u32(smem_u32(&bar.tmem_empty[0]), 0) : smem_u32(&bar.tmem_empty[0]);
+            auto release = [&](int buf) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) {
+                    if (T3_2CTA) mbar_arrive_cluster(rel_bar0 + buf * 8);
+                    else mbar_arrive(&bar.tmem_empty[buf]);
+                }
+            };
             const fs::PairScale ps = fs::pair_scale(operands, n_max, fa, fb);
             const float sc = ps.sc;
             T3Epi es;
@@ -384,7 +501,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
             if constexpr (SP) {
                 // write: row `lane`, 16-byte chunk cc at lane * 64 + ((cc ^ ((lane >> 1) & 3)) << 4)
                 // read : lane = parity * 16 + column pair cp; row 2 m + parity, word cp: chunk (cp >> 2) ^ (m & 3)
-                es.st_base = smem_u32(sB + T3_STAGES * T3_BOX_BYTES + 256) + warp * (T3_NBUF * T3_STAGE_BYTES);
+                es.st_base = smem_u32(sB + T3_STAGES * T3_B_STAGE_BYTES + 256) + warp * (T3_NBUF * T3_STAGE_BYTES);
                 const int cp = lane & 15, par = lane >> 4;
 #pragma unroll
                 for (int x = 0; x < 4; x++) {
@@ -397,17 +514,15 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                 const int slab = ((m0 + half * 128 + quarter * 32) >> 5) * 2 + par;
                 es.col_out = colraw + ((size_t)p * nslab + slab) * cpitch + 2 * cp;
             }
-            // a warp whose 32 rows all lie beyond n0 only keeps the accumulator hand-shake going
-            const bool warp_dead = m0 + half * 128 + quarter * 32 >= n0;
+            // a warp without rows (beyond n0, or an empty half) only keeps the accumulator hand-shake going
+            const bool warp_dead = ghost || half >= nhalf || m0 + half * 128 + quarter * 32 >= n0;
             for (int t = 0; t < ntiles; t++) {
                 const int buf = t & 1;
                 mbar_wait(&bar.tmem_full[buf], (t >> 1) & 1);
                 tc_fence_after();
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(70 + t);
                 if (warp_dead) {
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                    release(buf);
                     continue;
                 }
                 const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (buf * 2 + half) * T3_BN + csp * T3_CW;
@@ -423,9 +538,7 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
 #pragma unroll
                     for (int c = 0; c < T3_CW / 32; c++) tmem_ld_32x32b_x32(taddr + c * 32, rr[c]);
                     tmem_ld_wait();
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                    release(buf);
                     if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
                     if (probe & 2) {
                         es.k1 = max(es.k1, rr[0][0] ^ rr[T3_CW / 32 - 1][31]);
@@ -433,28 +546,29 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
                     }
 #pragma unroll
                     for (int c = 0; c < T3_CW / 32; c++) {
-                        if (masked) t3_chunk<MODE, true>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
-                        else t3_chunk<MODE, false>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        if (masked) t3_chunk<MODE, true>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es, [] {});
+                        else t3_chunk<MODE, false>(rr[c], tcol0 + c * 32, c, n1, sc, key_mul, es, [] {});
                     }
                 } else {
-                    // chunk by chunk (the register budget of 18 warps): the buffer goes back after the last chunk's load
+                    // chunk by chunk (the register budget of 18 warps holds one): the buffer goes back after the last
+                    // chunk's load.  (Fetching the second chunk into the first one's registers as soon as its keys exist,
+                    // so that the buffer returns while the first chunk's tournaments still run, measured SLOWER: 0.560
+                    // against 0.533 ms; so did a second staging tile per warp, 0.563 ms.)
                     uint32_t rr[32];
 #pragma unroll
                     for (int c = 0; c < T3_CW / 32; c++) {
                         tmem_ld_32x32b_x32(taddr + c * 32, rr);
                         tmem_ld_wait();
                         if (c == T3_CW / 32 - 1) {
-                            tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) mbar_arrive(&bar.tmem_empty[buf]);
+                            release(buf);
                             if (threadIdx.x == 0 && t < 20) T3_TRACE(110 + t);
                         }
                         if (probe & 2) {
                             es.k1 = max(es.k1, rr[0] ^ rr[31]);
                             continue;
                         }
-                        if (masked) t3_chunk<MODE, true>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
-                        else t3_chunk<MODE, false>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es);
+                        if (masked) t3_chunk<MODE, true>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es, [] {});
+                        else t3_chunk<MODE, false>(rr, tcol0 + c * 32, c, n1, sc, key_mul, es, [] {});
                     }
                 }
                 if (threadIdx.x == 0 && t < 20) T3_TRACE(90 + t);
@@ -482,7 +596,8 @@ k_float_top3_tc(const __grid_constant__ CUtensorMap tmap, const __grid_constant_
     cluster_sync_all();  // the peer may still be signalling this CTA's barriers
     if (warp == T3_MMA_WARP) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, T3_TMEM_COLS);
+        if (T3_2CTA) tmem_dealloc2(tmem_base, T3_TMEM_COLS);
+        else tmem_dealloc(tmem_base, T3_TMEM_COLS);
     }
 }
 
