@@ -150,7 +150,8 @@ int fs_float_match_knn(const void* operands_fp16, int n_frames, int n_max, const
                        int32_t* matches0, float* score0, float* second0, int32_t* n_matches, int32_t* diag,
                        void* workspace, size_t workspace_bytes, fs_stream_t stream);
 /* measurement hook: only the tensor-core kernel of fs_float_match (top-3 keys into the workspace).
- * probe = 0: the real kernel; bit 0: issue no MMAs; bit 1: skip the top-3 network (pipe-overlap experiments);
+ * probe = 0: the real kernel (the single-pass form where fs_float_match would run it); bit 0: issue no MMAs; bit 1: skip
+ * the top-3 / column network (pipe-overlap experiments); bit 2: the two-direction form;
  * trace: NULL, or 160 x i64 on the device: clock64() at the pipeline's hand-over points of the CTA of pair probe >> 8 */
 int fs_float_top3_keys(const void* operands_fp16, int n_frames, int n_max, const int32_t* counts,
                        const int32_t* pair_a, const int32_t* pair_b, int n_pairs, int probe, long long* trace,
