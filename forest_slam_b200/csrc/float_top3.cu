@@ -979,13 +979,11 @@ extern "C" size_t fs_float_operand_bytes(int n_frames, int n_max) {
     return (size_t)n_frames * fs::op_rows(n_max) * fs::OP_ROW_BYTES;
 }
 
-// FS_TUNE_FLOAT_SINGLE_PASS=0 keeps fs_float_match on the two-direction kernel (A/B measurements)
+// FS_TUNE_FLOAT_SINGLE_PASS=0 keeps fs_float_match on the two-direction kernel (A/B measurements, and the GPU test that
+// compares the two forms bit for bit); read on every call (host side only)
 static bool single_pass_enabled() {
-    static const bool on = [] {
-        const char* e = getenv("FS_TUNE_FLOAT_SINGLE_PASS");
-        return !(e && e[0] == '0');
-    }();
-    return on;
+    const char* e = getenv("FS_TUNE_FLOAT_SINGLE_PASS");
+    return !(e && e[0] == '0');
 }
 
 extern "C" size_t fs_float_match_tc_workspace_bytes(int n_pairs, int n_max) {

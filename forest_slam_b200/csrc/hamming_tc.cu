@@ -133,13 +133,11 @@ k_hamming_colmerge(int n_max, const int32_t* __restrict__ counts, const int32_t*
     keys1[(size_t)p * n_max + t] = make_uint4(best, 0u, 0u, 0u);
 }
 
-// FS_TUNE_HAMMING_SINGLE_PASS=0 keeps fs_hamming_match_tc on the two-direction kernel (A/B measurements)
+// FS_TUNE_HAMMING_SINGLE_PASS=0 keeps fs_hamming_match_tc on the two-direction kernel (A/B measurements, tests); read on
+// every call (host side only)
 bool hamming_single_pass_enabled() {
-    static const bool on = [] {
-        const char* e = getenv("FS_TUNE_HAMMING_SINGLE_PASS");
-        return !(e && e[0] == '0');
-    }();
-    return on;
+    const char* e = getenv("FS_TUNE_HAMMING_SINGLE_PASS");
+    return !(e && e[0] == '0');
 }
 
 }  // namespace

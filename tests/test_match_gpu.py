@@ -282,3 +282,95 @@ def test_float_knn_ratio_without_cross_check(fsb):
             if q in got_r:
                 assert got_r[q] == pair[0].trainIdx
     assert 50 < len(got_r) < 700
+
+
+def _with_env(name, value, fn):
+    old = os.environ.get(name)
+    os.environ[name] = value
+    try:
+        return fn()
+    finally:
+        if old is None:
+            del os.environ[name]
+        else:
+            os.environ[name] = old
+
+
+@pytest.mark.parametrize("kind", ["forest", "random", "ragged_duplicates"])
+def test_float_single_pass_equals_two_direction_form(fsb, kind):
+    """fs_float_match's single pass (column side from packed 16-bit slab maxima, certified by k_float_colcheck) against
+    the two-direction form (one tensor-core pass per direction, every row certified on its own): every index output bit for
+    bit, the scores where both are exact, at the bench's size (2048 keypoints) and on ragged banks with duplicated rows."""
+    import torch
+    n = 2048
+    rng = np.random.default_rng(77)
+    if kind == "ragged_duplicates":
+        counts = [n, n - 37, 1, 0, 655, 2, 129, 1900]
+        F = len(counts)
+        desc = rng.standard_normal((F, 256, n)).astype(np.float32)
+        desc /= np.linalg.norm(desc, axis=1, keepdims=True)
+        desc[1, :, :600] = desc[0, :, 50:650]                         # shared rows (exact copies)
+        desc[1, :, 600:640] = desc[1, :, :1]                          # 41 identical rows in one frame: lowest index wins
+        desc[4, :, :300] = desc[1, :, :300]
+        desc[7, :, :1500] = desc[0, :, :1500] + 1e-4 * rng.standard_normal((256, 1500)).astype(np.float32)
+        desc[7] /= np.linalg.norm(desc[7], axis=0, keepdims=True)
+        pa = [0, 1, 1, 4, 4, 2, 3, 0, 5, 0, 2, 7, 0, 6]
+        pb = [1, 0, 4, 1, 4, 0, 1, 3, 0, 5, 2, 0, 7, 7]
+        for f, c in enumerate(counts):
+            desc[f, :, c:] = 0
+    else:
+        F = 9
+        counts = [n] * F
+        if kind == "forest":
+            base = rng.standard_normal((256, 3 * n)).astype(np.float32)
+            base /= np.linalg.norm(base, axis=0, keepdims=True)
+            desc = np.empty((F, 256, n), np.float32)
+            for f in range(F):  # consecutive frames share 70 % of their landmarks, observed with noise
+                cols = (np.arange(n) + f * (3 * n // 10)) % (3 * n)
+                d = base[:, rng.permutation(cols)] + 0.05 * rng.standard_normal((256, n)).astype(np.float32)
+                desc[f] = d / np.linalg.norm(d, axis=0, keepdims=True)
+        else:
+            desc = rng.standard_normal((F, 256, n)).astype(np.float32)
+            desc /= np.linalg.norm(desc, axis=1, keepdims=True)
+        pa, pb = list(range(F - 1)), list(range(1, F))
+    bank = torch.from_numpy(desc).cuda()
+    cnt = torch.tensor(counts, dtype=torch.int32).cuda()
+    ops = fsb.float_prepare(bank, cnt)
+    for thr, ratio in [(None, None), (0.2, 0.9)]:
+        run = lambda: fsb.float_match_batch(None, cnt, pa, pb, operands=ops, threshold=thr, ratio=ratio, want_diag=True)
+        sp = run()
+        two = _with_env("FS_TUNE_FLOAT_SINGLE_PASS", "0", run)
+        assert int(sp["diag"][2]) + int(sp["diag"][3]) >= 0 and int(two["diag"][2]) == 0  # the second run was the other form
+        for key in ("matches0", "matches1", "n_matches"):
+            assert torch.equal(sp[key], two[key]), (kind, key, thr, ratio)
+        # scores: identical wherever a decision depended on them (both forms rescore those exactly); elsewhere both are
+        # the same tensor-core value
+        assert torch.equal(sp["score0"], two["score0"]), (kind, thr, ratio)
+    if kind == "forest":
+        assert int(sp["n_matches"].min()) > n // 3
+
+
+def test_hamming_single_pass_equals_two_direction_form(fsb):
+    """fs_hamming_match_tc in a single pass (train rows' best queries folded from the slab maxima) against the
+    two-direction form, on the stereo workload's shape (2000 keypoints: not a multiple of the 128-column tile)."""
+    import torch
+    n = 2000
+    rng = np.random.default_rng(5)
+    F = 6
+    bank = rng.integers(0, 256, (F, n, 32), dtype=np.uint8)
+    for f in range(1, F):
+        k = 1400
+        bank[f, :k] = bank[f - 1, 300:300 + k] ^ np.packbits(rng.random((k, 256)) < 0.06, axis=1)
+    bank[3, 1500:1540] = bank[3, 7]  # identical rows: lowest index wins in both directions
+    counts = [n, n, 1999, n, 1234, n]
+    dev_bank = torch.from_numpy(bank).cuda()
+    cnt = torch.tensor(counts, dtype=torch.int32).cuda()
+    ops = fsb.hamming_prepare(dev_bank, cnt)
+    pa, pb = [0, 1, 2, 3, 4, 3, 5], [1, 2, 3, 4, 5, 3, 0]
+    for ratio in (None, 0.8):
+        run = lambda: fsb.hamming_match_batch(None, cnt, pa, pb, cross_check=True, ratio=ratio, operands=ops)
+        sp = run()
+        two = _with_env("FS_TUNE_HAMMING_SINGLE_PASS", "0", run)
+        for key in ("matches0", "dist0", "second0", "matches1", "n_matches"):
+            assert torch.equal(sp[key], two[key]), (key, ratio)
+    assert int(sp["n_matches"][0]) > 0
