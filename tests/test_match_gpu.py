@@ -374,3 +374,61 @@ def test_hamming_single_pass_equals_two_direction_form(fsb):
         for key in ("matches0", "dist0", "second0", "matches1", "n_matches"):
             assert torch.equal(sp[key], two[key]), (key, ratio)
     assert int(sp["n_matches"][0]) > 0
+
+
+def test_matchers_stay_inside_their_workspace(fsb):
+    """The single-pass matchers carve row keys, column keys and the slab results out of the caller's workspace: guard bytes
+    on both sides of it (and of every output array) must survive ragged banks whose last row group / last column tile is
+    partial (compute-sanitizer is closed on this pool, so the bounds are checked with canaries)."""
+    import torch
+    from forest_slam_b200 import _lib
+    lib = _lib.load()
+    G = 1 << 16
+    rng = np.random.default_rng(9)
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def guarded(nbytes):
+        buf = torch.full((nbytes + 2 * G,), 0xA5, dtype=torch.uint8, device="cuda")
+        return buf, buf.data_ptr() + G
+
+    def intact(buf, nbytes):
+        return bool((buf[:G] == 0xA5).all()) and bool((buf[G + nbytes:] == 0xA5).all())
+
+    pa = torch.tensor([0, 1, 2, 3, 1], dtype=torch.int32, device="cuda")
+    pb = torch.tensor([1, 2, 3, 0, 1], dtype=torch.int32, device="cuda")
+    P = 5
+    # ---- float, n_max = 640 (a multiple of 128 that is not a multiple of 256: the second CTA of the last cluster has
+    # one empty half), ragged counts
+    n = 640
+    counts = torch.tensor([n, n - 33, 257, 1], dtype=torch.int32, device="cuda")
+    desc = rng.standard_normal((4, 256, n)).astype(np.float32)
+    desc /= np.linalg.norm(desc, axis=1, keepdims=True)
+    ops = fsb.float_prepare(torch.from_numpy(desc).cuda(), counts)
+    need = int(lib.fs_float_match_tc_workspace_bytes(P, n))
+    ws, ws_ptr = guarded(need)
+    outs = {k: guarded(P * n * 4) for k in ("m0", "sc", "se", "m1")}
+    nm, nm_ptr = guarded(P * 4)
+    _lib.check(lib.fs_float_match(ops.data_ptr(), 4, n, counts.data_ptr(), pa.data_ptr(), pb.data_ptr(), P, 1.0,
+                                  float("-inf"), 0.0, outs["m0"][1], outs["sc"][1], outs["se"][1], outs["m1"][1], nm_ptr,
+                                  None, ws_ptr, need, stream), "fs_float_match")
+    torch.cuda.synchronize()
+    assert intact(ws, need) and intact(nm, P * 4)
+    assert all(intact(b, P * n * 4) for b, _ in outs.values())
+    # ---- Hamming, n_max = 1000 (no multiple of 32 or 128)
+    n = 1000
+    counts = torch.tensor([n, n - 7, 33, 1], dtype=torch.int32, device="cuda")
+    bank = torch.from_numpy(rng.integers(0, 256, (4, n, 32), dtype=np.uint8)).cuda()
+    hops = fsb.hamming_prepare(bank, counts)
+    need = int(lib.fs_hamming_match_tc_workspace_bytes(P, n))
+    ws, ws_ptr = guarded(need)
+    outs = {k: guarded(P * n * 4) for k in ("m0", "d0", "s0", "m1")}
+    nm, nm_ptr = guarded(P * 4)
+    _lib.check(lib.fs_hamming_match_tc(hops.data_ptr(), 4, n, counts.data_ptr(), pa.data_ptr(), pb.data_ptr(), P, 1, 0.0,
+                                       outs["m0"][1], outs["d0"][1], outs["s0"][1], outs["m1"][1], nm_ptr, ws_ptr, need,
+                                       stream), "fs_hamming_match_tc")
+    torch.cuda.synchronize()
+    assert intact(ws, need) and intact(nm, P * 4)
+    assert all(intact(b, P * n * 4) for b, _ in outs.values())
+    ref = fsb.hamming_match_batch(bank, counts, pa, pb, cross_check=True, popc=True)
+    got = outs["m0"][0][G:G + P * n * 4].view(torch.int32).view(P, n)
+    assert torch.equal(got, ref["matches0"])
