@@ -432,3 +432,37 @@ def test_matchers_stay_inside_their_workspace(fsb):
     ref = fsb.hamming_match_batch(bank, counts, pa, pb, cross_check=True, popc=True)
     got = outs["m0"][0][G:G + P * n * 4].view(torch.int32).view(P, n)
     assert torch.equal(got, ref["matches0"])
+
+
+def test_float_single_pass_every_block_shape(fsb):
+    """Row counts on both sides of every 32 / 128 / 256 / 512 boundary (a cluster = two CTAs of 256 rows: empty second
+    half, ghost peer, partial last row group) and column counts on both sides of the 32 / 128 boundaries: the single-pass
+    CTA-pair kernel against the two-direction form, bit for bit, and against the fp64 oracle on one pair per shape."""
+    import torch
+    n = 1024
+    sizes = [1, 31, 32, 33, 127, 128, 129, 255, 256, 257, 383, 384, 385, 511, 512, 513, 640, 767, 768, 769, 1000, 1023, 1024]
+    F = len(sizes)
+    rng = np.random.default_rng(2024)
+    base = rng.standard_normal((256, n)).astype(np.float32)
+    base /= np.linalg.norm(base, axis=0, keepdims=True)
+    desc = np.zeros((F, 256, n), np.float32)
+    for f, c in enumerate(sizes):
+        d = base[:, rng.permutation(n)[:c]] + 0.03 * rng.standard_normal((256, c)).astype(np.float32)
+        desc[f, :, :c] = d / np.linalg.norm(d, axis=0, keepdims=True)
+    pa = list(range(F)) + list(range(F))
+    pb = [(f * 7 + 3) % F for f in range(F)] + [F - 1 - f for f in range(F)]
+    bank = torch.from_numpy(desc).cuda()
+    cnt = torch.tensor(sizes, dtype=torch.int32).cuda()
+    ops = fsb.float_prepare(bank, cnt)
+    run = lambda: fsb.float_match_batch(None, cnt, pa, pb, operands=ops, ratio=0.95, want_diag=True)
+    sp = run()
+    two = _with_env("FS_TUNE_FLOAT_SINGLE_PASS", "0", run)
+    for key in ("matches0", "matches1", "n_matches", "score0"):
+        assert torch.equal(sp[key], two[key]), key
+    m0 = sp["matches0"].cpu().numpy()
+    for k in range(0, len(pa), 5):
+        a, b = pa[k], pb[k]
+        ref = lit.float_mutual_nn(desc[a][:, :sizes[a]], desc[b][:, :sizes[b]], ratio=0.95)
+        keep = ~ref["ambiguous0"]
+        assert np.array_equal(m0[k, :sizes[a]][keep], ref["matches0"][keep]), (sizes[a], sizes[b])
+        assert np.all(m0[k, sizes[a]:] == -1)
