@@ -447,6 +447,16 @@ struct EPnP {
     }
     template <class PA, class PW>
     CVM_HD void compute_pose_ws(double* R_out, double* t_out, PA ut, PW d) {
+        double ut8[4 * 12];
+        compute_basis_ws<PA, PW>(ut, d, ut8);
+        compute_pose_from_basis(ut8, R_out, t_out);
+    }
+
+    // First half of epnp::compute_pose: control points, barycentric coordinates, M^T M and its 12x12 decomposition.
+    // ut8 = rows 8..11 of U^T, the only part the second half reads.  (The RANSAC solver kernel runs the two halves as two
+    // launches: only this one needs the 1.25 KB per-thread matrix workspace that limits it to four warps per SM.)
+    template <class PA, class PW>
+    CVM_HD void compute_basis_ws(PA ut, PW d, double* ut8) {
         choose_control_points();
         compute_barycentric_coordinates();
         double M[2 * NP * 12];
@@ -477,8 +487,11 @@ struct EPnP {
         // (WAVEFRONT = true is bit-identical — 104/104 parity tests — but measured SLOWER on B200: PnP stage 8.0 ms against
         // 6.4 ms per 256 pairs; the six predicated chains cost more issue slots and address arithmetic than they hide)
         jacobi_svd<12, 12, 12, /*KEEP_V*/ false, PA, PW, /*WAVEFRONT*/ false>(ut, 12, d, nullptr);
-        double ut8[4 * 12];
         for (int i = 0; i < 48; i++) ut8[i] = ut[96 + i];
+    }
+
+    // Second half: the three beta approximations, Gauss-Newton, absolute orientation, best reprojection error.
+    CVM_HD void compute_pose_from_basis(const double* ut8, double* R_out, double* t_out) {
         double l_6x10[60], rho[6];
         compute_L_6x10(ut8, l_6x10);
         compute_rho(rho);
@@ -499,6 +512,28 @@ struct EPnP {
             t_out[i] = ts[N][i];
             for (int j = 0; j < 3; j++) R_out[3 * i + j] = Rs[N][i][j];
         }
+    }
+
+    // What the second half needs of the first, as a flat record (RANSAC solver, two launches): 15 + 10 + 20 + 12 + 48.
+    static constexpr int STATE_DOUBLES = NP * 3 + NP * 2 + NP * 4 + 12 + 48;
+    CVM_HD void save_state(const double* ut8, double* st) const {
+        int o = 0;
+        for (int i = 0; i < NP * 3; i++) st[o++] = pws[i];
+        for (int i = 0; i < NP * 2; i++) st[o++] = us[i];
+        for (int i = 0; i < NP * 4; i++) st[o++] = alphas[i];
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 3; j++) st[o++] = cws[i][j];
+        for (int i = 0; i < 48; i++) st[o++] = ut8[i];
+    }
+    CVM_HD void load_state(const CamD& cam, const double* st, double* ut8) {
+        fu = cam.fx; fv = cam.fy; uc = cam.cx; vc = cam.cy;
+        int o = 0;
+        for (int i = 0; i < NP * 3; i++) pws[i] = st[o++];
+        for (int i = 0; i < NP * 2; i++) us[i] = st[o++];
+        for (int i = 0; i < NP * 4; i++) alphas[i] = st[o++];
+        for (int i = 0; i < 4; i++)
+            for (int j = 0; j < 3; j++) cws[i][j] = st[o++];
+        for (int i = 0; i < 48; i++) ut8[i] = st[o++];
     }
 };
 
@@ -553,6 +588,29 @@ CVM_HD void pnp_minimal_epnp5_ws(const CamD& cam, const double (*obj)[3], const 
     e.init(cam, obj, nrm);
     double R[9], t[3];
     e.template compute_pose_ws<PA, PW>(R, t, ut, d);
+    rodrigues_mat2vec(R, model);
+    model[3] = t[0];
+    model[4] = t[1];
+    model[5] = t[2];
+}
+
+// the same in two halves (ransac_pnp.cu): `state` = EPnP<5>::STATE_DOUBLES doubles per solve
+template <class PA, class PW>
+CVM_HD void pnp_minimal_epnp5_basis(const CamD& cam, const double (*obj)[3], const float (*img)[2], double* state, PA ut,
+                                    PW d) {
+    float nrm[5][2];
+    for (int i = 0; i < 5; i++) undistort_point_f32(img[i][0], img[i][1], cam, nrm[i][0], nrm[i][1]);
+    EPnP<5> e;
+    e.init(cam, obj, nrm);
+    double ut8[48];
+    e.template compute_basis_ws<PA, PW>(ut, d, ut8);
+    e.save_state(ut8, state);
+}
+CVM_HD void pnp_minimal_epnp5_finish(const CamD& cam, const double* state, double* model) {
+    EPnP<5> e;
+    double ut8[48], R[9], t[3];
+    e.load_state(cam, state, ut8);
+    e.compute_pose_from_basis(ut8, R, t);
     rodrigues_mat2vec(R, model);
     model[3] = t[0];
     model[4] = t[1];

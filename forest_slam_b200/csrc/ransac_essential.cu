@@ -78,8 +78,11 @@ struct EPolicy {
     };
     static constexpr int SOLVE_THREADS = 64;
     static constexpr int SOLVE_SMEM_DOUBLES = 0;  // the five-point solver keeps its state in registers / local memory
+    static constexpr int STATE_DOUBLES = 0;       // one launch per solve
+    static constexpr int SOLVE2_THREADS = 64;
+    __device__ static int solve2(const Params&, const double*, double*) { return 0; }
     __device__ static int solve(const Params& prm, int p, const int* sub, double* models, int slot, Tail* tail,
-                                int* n_tail, double*) {
+                                int* n_tail, double*, double*) {
         const double* src = prm.pts + (size_t)p * 4 * prm.n_max;
         double q1[5][2], q2[5][2];
 #pragma unroll

@@ -112,6 +112,7 @@ struct Workspace {
     int* slot_counts;   // [pool][MAXM]
     double* slot_models;  // [pool][MAXM][MD]
     typename Pol::Tail* tail;  // [TAIL_CAP]
+    double* slot_state;  // [pool][Pol::STATE_DOUBLES]: what a two-launch solver hands from its first half to its second
     static size_t bytes(int n_pairs, const Plan& pl) {
         size_t b = 0;
         auto add = [&](size_t x) { b = fs::align_up(b, 256) + x; };
@@ -123,6 +124,7 @@ struct Workspace {
         add(pl.pool * Pol::MAXM * sizeof(int));
         add(pl.pool * Pol::MAXM * Pol::MD * sizeof(double));
         add((size_t)TAIL_CAP * sizeof(typename Pol::Tail));
+        add(pl.pool * (size_t)Pol::STATE_DOUBLES * sizeof(double));
         return fs::align_up(b, 256);
     }
     void carve(fs::Carver& c, int n_pairs, const Plan& pl) {
@@ -134,6 +136,7 @@ struct Workspace {
         slot_counts = c.take<int>(pl.pool * Pol::MAXM);
         slot_models = c.take<double>(pl.pool * Pol::MAXM * Pol::MD);
         tail = c.take<typename Pol::Tail>(TAIL_CAP);
+        slot_state = c.take<double>(pl.pool * (size_t)Pol::STATE_DOUBLES);
     }
 };
 
@@ -290,9 +293,22 @@ k_rg_solve(int round, typename Pol::Params prm, Workspace<Pol> ws) {
 #pragma unroll
         for (int i = 0; i < Pol::MP; i++) sub[i] = ws.slot_subset[(size_t)slot * Pol::MP + i];
         const int nm = Pol::solve(prm, p, sub, ws.slot_models + (size_t)slot * Pol::MAXM * Pol::MD, slot, ws.tail,
-                                  &ws.ctl[round].n_tail, rg_solve_smem + threadIdx.x);
-        if (nm >= 0) ws.slot_nmodels[slot] = nm;  // < 0: deferred to k_rg_tail
+                                  &ws.ctl[round].n_tail, rg_solve_smem + threadIdx.x,
+                                  ws.slot_state + (size_t)slot * Pol::STATE_DOUBLES);
+        if (nm >= 0) ws.slot_nmodels[slot] = nm;  // < 0: deferred to k_rg_tail / finished by k_rg_solve2
     }
+}
+
+// second half of a two-launch solver (Pol::STATE_DOUBLES > 0): one thread per slot, no shared memory, so that it runs
+// at the occupancy the registers allow while the first half is held to the warps its per-thread matrices leave room for
+template <class Pol>
+__global__ void __launch_bounds__(Pol::SOLVE2_THREADS)
+k_rg_solve2(int round, typename Pol::Params prm, Workspace<Pol> ws) {
+    const int used = ws.ctl[round].n_used;
+    const int slot = blockIdx.x * Pol::SOLVE2_THREADS + threadIdx.x;
+    if (slot >= used || ws.slot_pair[slot] < 0) return;
+    ws.slot_nmodels[slot] = Pol::solve2(prm, ws.slot_state + (size_t)slot * Pol::STATE_DOUBLES,
+                                        ws.slot_models + (size_t)slot * Pol::MAXM * Pol::MD);
 }
 
 // solves the solve pass suspended (rare, long-running): one WARP per deferred solve.  One warp per CTA so that the
@@ -367,6 +383,8 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
         if (!hinted[dev]) {
             if (Pol::SOLVE_SMEM_DOUBLES == 0 && tune("FS_TUNE_CARVEOUT", 1) == 1)
                 FS_CUDA(cudaFuncSetAttribute(k_rg_solve<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
+            if (Pol::STATE_DOUBLES > 0 && tune("FS_TUNE_CARVEOUT", 1) == 1)
+                FS_CUDA(cudaFuncSetAttribute(k_rg_solve2<Pol>, cudaFuncAttributePreferredSharedMemoryCarveout, 0));
             hinted[dev] = true;
         }
     }
@@ -402,6 +420,12 @@ int run_rounds(int n_pairs, const int32_t* n_corr, int n_max, int min_points, in
         if (Pol::HAS_TAIL) {
             k_rg_tail<Pol><<<256, 32, 0, stream>>>(r, prm, ws);
             FS_LAUNCH_CHECK("k_rg_tail");
+        }
+        if constexpr (Pol::STATE_DOUBLES > 0) {
+            // round 0 uses first_chunk slots per pair at most; later rounds the whole pool
+            const int slots = (r == 0) ? min(pool, n_pairs * ((pl.first_chunk + Pol::SLAB - 1) / Pol::SLAB * Pol::SLAB)) : pool;
+            k_rg_solve2<Pol><<<(slots + Pol::SOLVE2_THREADS - 1) / Pol::SOLVE2_THREADS, Pol::SOLVE2_THREADS, 0, stream>>>(r, prm, ws);
+            FS_LAUNCH_CHECK("k_rg_solve2");
         }
         // round 0 uses first_chunk slots per pair at most
         const int sg = (r == 0) ? min(score_grid, (n_pairs * pl.first_chunk + Pol::SLAB - 1) / Pol::SLAB) : score_grid;

@@ -121,8 +121,22 @@ struct PPolicy {
     // (measured: CTAs of 32 threads so that five solver warps fit an SM are SLOWER — 33.3k pairs/s at four warps, 31k at
     // five, against 37k for two CTAs of 64: a fifth warp doubles up on one SM sub-partition and stretches the critical path)
     static constexpr int SOLVE_THREADS = 64;
+    // Two launches per solve: the first half (undistort, control points, M^T M, the 12x12 Jacobi SVD: 57 % of the solver)
+    // needs the shared-memory matrices and is held to four warps per SM by them; the second half (three beta
+    // approximations x Gauss-Newton, absolute orientation, Rodrigues) needs none and runs at eight warps per SM.
+    static constexpr int STATE_DOUBLES = cvm::EPnP<5>::STATE_DOUBLES;
+    static constexpr int SOLVE2_THREADS = 64;
+    __device__ static int solve2(const Params& prm, const double* state, double* model) {
+        double st[STATE_DOUBLES], m[6];
+#pragma unroll 1
+        for (int i = 0; i < STATE_DOUBLES; i++) st[i] = state[i];
+        cvm::pnp_minimal_epnp5_finish(prm.cam, st, m);
+#pragma unroll
+        for (int i = 0; i < 6; i++) model[i] = m[i];
+        return 1;
+    }
     __device__ static int solve(const Params& prm, int p, const int* sub, double* model, int, Tail*, int*,
-                                double* smem) {
+                                double* smem, double* state) {
         const float* p3 = prm.points3d + 3 * (size_t)p * prm.n_max;
         const float2* p2 = reinterpret_cast<const float2*>(prm.pts2d) + (size_t)p * prm.n_max;
         double obj[5][3];
@@ -137,12 +151,12 @@ struct PPolicy {
             img[i][0] = q.x;
             img[i][1] = q.y;
         }
-        double m[6];
         using SP = cvm::Strided<SOLVE_THREADS>;
-        cvm::pnp_minimal_epnp5_ws<SP, SP>(prm.cam, obj, img, m, SP{smem}, SP{smem + 144 * SOLVE_THREADS});
-#pragma unroll
-        for (int i = 0; i < 6; i++) model[i] = m[i];
-        return 1;
+        double st[STATE_DOUBLES];
+        cvm::pnp_minimal_epnp5_basis<SP, SP>(prm.cam, obj, img, st, SP{smem}, SP{smem + 144 * SOLVE_THREADS});
+#pragma unroll 1
+        for (int i = 0; i < STATE_DOUBLES; i++) state[i] = st[i];
+        return -1;  // finished by k_rg_solve2
     }
     __device__ static int solve_tail(const Params&, Tail&, double*) { return 0; }
     struct Scorer {
