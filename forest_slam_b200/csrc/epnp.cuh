@@ -459,27 +459,21 @@ struct EPnP {
     CVM_HD void compute_basis_ws(PA ut, PW d, double* ut8) {
         choose_control_points();
         compute_barycentric_coordinates();
-        double M[2 * NP * 12];
-        for (int i = 0; i < NP; i++) {
-            const double* as = alphas + 4 * i;
-            const double u = us[2 * i], v = us[2 * i + 1];
-            double* M1 = M + (2 * i) * 12;
-            double* M2 = M1 + 12;
-            for (int k = 0; k < 4; k++) {
-                M1[3 * k] = as[k] * fu;
-                M1[3 * k + 1] = 0.0;
-                M1[3 * k + 2] = as[k] * (uc - u);
-                M2[3 * k] = 0.0;
-                M2[3 * k + 1] = as[k] * fv;
-                M2[3 * k + 2] = as[k] * (vc - v);
-            }
-        }
+        // M (2 NP x 12): rows 2i / 2i+1 = alphas_i[k] * (fu, 0, uc - u_i) / (0, fv, vc - v_i) for the four control points k.
+        // Its entries are recomputed where MtM needs them (one multiply each, the same bits every time) instead of being
+        // kept as a 960-byte local array: the solver kernel is bound by what it keeps in local memory.
+        auto Mkc = [&](int k, int c) -> double {
+            const double a = alphas[4 * (k >> 1) + c / 3];
+            const int comp = c % 3;
+            if ((k & 1) == 0) return comp == 0 ? a * fu : comp == 1 ? 0.0 : a * (uc - us[2 * (k >> 1)]);
+            return comp == 0 ? 0.0 : comp == 1 ? a * fv : a * (vc - us[2 * (k >> 1) + 1]);
+        };
         // MtM = M^T M (mulTransposed order: upper triangle, k ascending, completeSymm); it is symmetric, so the
         // transpose OpenCV hands to JacobiSVD is MtM itself: rows of At end as U^T
         for (int i = 0; i < 12; i++)
             for (int j = i; j < 12; j++) {
                 double s = 0;
-                for (int k = 0; k < 2 * NP; k++) s += M[k * 12 + i] * M[k * 12 + j];
+                for (int k = 0; k < 2 * NP; k++) s += Mkc(k, i) * Mkc(k, j);
                 ut[i * 12 + j] = s;
                 ut[j * 12 + i] = s;
             }
@@ -514,18 +508,19 @@ struct EPnP {
         }
     }
 
-    // What the second half needs of the first, as a flat record (RANSAC solver, two launches): 15 + 10 + 20 + 12 + 48.
-    static constexpr int STATE_DOUBLES = NP * 3 + NP * 2 + NP * 4 + 12 + 48;
-    CVM_HD void save_state(const double* ut8, double* st) const {
+    // What the second half needs of the first, as a flat record (RANSAC solver, two launches): 15 + 10 + 20 + 12 doubles of
+    // the problem (STATE_HEAD), then ut8 (48).
+    static constexpr int STATE_HEAD = NP * 3 + NP * 2 + NP * 4 + 12;
+    static constexpr int STATE_DOUBLES = STATE_HEAD + 48;
+    CVM_HD void save_state_head(double* st) const {
         int o = 0;
         for (int i = 0; i < NP * 3; i++) st[o++] = pws[i];
         for (int i = 0; i < NP * 2; i++) st[o++] = us[i];
         for (int i = 0; i < NP * 4; i++) st[o++] = alphas[i];
         for (int i = 0; i < 4; i++)
             for (int j = 0; j < 3; j++) st[o++] = cws[i][j];
-        for (int i = 0; i < 48; i++) st[o++] = ut8[i];
     }
-    CVM_HD void load_state(const CamD& cam, const double* st, double* ut8) {
+    CVM_HD void load_state_head(const CamD& cam, const double* st) {
         fu = cam.fx; fv = cam.fy; uc = cam.cx; vc = cam.cy;
         int o = 0;
         for (int i = 0; i < NP * 3; i++) pws[i] = st[o++];
@@ -533,7 +528,6 @@ struct EPnP {
         for (int i = 0; i < NP * 4; i++) alphas[i] = st[o++];
         for (int i = 0; i < 4; i++)
             for (int j = 0; j < 3; j++) cws[i][j] = st[o++];
-        for (int i = 0; i < 48; i++) ut8[i] = st[o++];
     }
 };
 
@@ -594,7 +588,8 @@ CVM_HD void pnp_minimal_epnp5_ws(const CamD& cam, const double (*obj)[3], const 
     model[5] = t[2];
 }
 
-// the same in two halves (ransac_pnp.cu): `state` = EPnP<5>::STATE_DOUBLES doubles per solve
+// the same in two halves (ransac_pnp.cu): `state` = EPnP<5>::STATE_DOUBLES doubles per solve, written / read in place
+// (global memory in the solver kernels: no local copy)
 template <class PA, class PW>
 CVM_HD void pnp_minimal_epnp5_basis(const CamD& cam, const double (*obj)[3], const float (*img)[2], double* state, PA ut,
                                     PW d) {
@@ -602,15 +597,14 @@ CVM_HD void pnp_minimal_epnp5_basis(const CamD& cam, const double (*obj)[3], con
     for (int i = 0; i < 5; i++) undistort_point_f32(img[i][0], img[i][1], cam, nrm[i][0], nrm[i][1]);
     EPnP<5> e;
     e.init(cam, obj, nrm);
-    double ut8[48];
-    e.template compute_basis_ws<PA, PW>(ut, d, ut8);
-    e.save_state(ut8, state);
+    e.template compute_basis_ws<PA, PW>(ut, d, state + EPnP<5>::STATE_HEAD);
+    e.save_state_head(state);
 }
 CVM_HD void pnp_minimal_epnp5_finish(const CamD& cam, const double* state, double* model) {
     EPnP<5> e;
-    double ut8[48], R[9], t[3];
-    e.load_state(cam, state, ut8);
-    e.compute_pose_from_basis(ut8, R, t);
+    double R[9], t[3];
+    e.load_state_head(cam, state);
+    e.compute_pose_from_basis(state + EPnP<5>::STATE_HEAD, R, t);
     rodrigues_mat2vec(R, model);
     model[3] = t[0];
     model[4] = t[1];

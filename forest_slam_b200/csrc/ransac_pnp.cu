@@ -92,7 +92,7 @@ struct PPolicy {
     static constexpr int FIRST_CHUNK = 192;        // speculative iterations per pair in round 0 (~390 are typical)
     static constexpr int FIRST_CHUNK_MIN = 192;    // (no batch-size dependence: the sweep is flat, profiles/README.md)
     static constexpr int SOLVE_WARPS_PER_SM = 4;  // solver warps per SM (ransac_grid.cuh: run_rounds)
-    static constexpr int SOLVE_WARPS_PER_SM_MAX = 4;  // two CTAs of 64 fill the SM's shared memory (78 KB each)
+    static constexpr int SOLVE_WARPS_PER_SM_MAX = 6;  // three CTAs of 64 fill the SM's shared memory (72 KB each)
     static constexpr const char* TUNE_FIRST = "FS_TUNE_P_FIRST_CHUNK";
     static constexpr const char* TUNE_WARPS = "FS_TUNE_P_SOLVE_WARPS";
     static constexpr int MP = 5;
@@ -116,8 +116,8 @@ struct PPolicy {
         st.carve(smem, prm.n_max);
         st.load(prm.points3d + 3 * (size_t)p * prm.n_max, prm.pts2d + 2 * (size_t)p * prm.n_max, n);
     }
-    // 12x12 U^T + 12 singular values of EPnP's decomposition, per solver thread, in shared memory (78 KB per CTA of 64)
-    static constexpr int SOLVE_SMEM_DOUBLES = 156;
+    // 12x12 U^T of EPnP's decomposition, per solver thread, in shared memory (72 KB per CTA of 64: three CTAs per SM)
+    static constexpr int SOLVE_SMEM_DOUBLES = 144;
     // (measured: CTAs of 32 threads so that five solver warps fit an SM are SLOWER — 33.3k pairs/s at four warps, 31k at
     // five, against 37k for two CTAs of 64: a fifth warp doubles up on one SM sub-partition and stretches the critical path)
     static constexpr int SOLVE_THREADS = 64;
@@ -127,10 +127,8 @@ struct PPolicy {
     static constexpr int STATE_DOUBLES = cvm::EPnP<5>::STATE_DOUBLES;
     static constexpr int SOLVE2_THREADS = 64;
     __device__ static int solve2(const Params& prm, const double* state, double* model) {
-        double st[STATE_DOUBLES], m[6];
-#pragma unroll 1
-        for (int i = 0; i < STATE_DOUBLES; i++) st[i] = state[i];
-        cvm::pnp_minimal_epnp5_finish(prm.cam, st, m);
+        double m[6];
+        cvm::pnp_minimal_epnp5_finish(prm.cam, state, m);
 #pragma unroll
         for (int i = 0; i < 6; i++) model[i] = m[i];
         return 1;
@@ -152,10 +150,8 @@ struct PPolicy {
             img[i][1] = q.y;
         }
         using SP = cvm::Strided<SOLVE_THREADS>;
-        double st[STATE_DOUBLES];
-        cvm::pnp_minimal_epnp5_basis<SP, SP>(prm.cam, obj, img, st, SP{smem}, SP{smem + 144 * SOLVE_THREADS});
-#pragma unroll 1
-        for (int i = 0; i < STATE_DOUBLES; i++) state[i] = st[i];
+        double w[12];  // the singular values: 96 B of local memory, so that the matrix alone sets the shared-memory footprint
+        cvm::pnp_minimal_epnp5_basis<SP, double*>(prm.cam, obj, img, state, SP{smem}, w);
         return -1;  // finished by k_rg_solve2
     }
     __device__ static int solve_tail(const Params&, Tail&, double*) { return 0; }
