@@ -21,6 +21,10 @@
 #include "pnpmath.cuh"
 #include "posemath.cuh"
 
+#ifndef EPNP_WAVEFRONT
+#define EPNP_WAVEFRONT false
+#endif
+
 namespace cvm {
 
 // ---------------------------------------------------------------------------------------- building blocks
@@ -478,9 +482,10 @@ struct EPnP {
                 ut[j * 12 + i] = s;
             }
         // V is not an output of epnp's cvSVD call
-        // (WAVEFRONT = true is bit-identical — 104/104 parity tests — but measured SLOWER on B200: PnP stage 8.0 ms against
-        // 6.4 ms per 256 pairs; the six predicated chains cost more issue slots and address arithmetic than they hide)
-        jacobi_svd<12, 12, 12, /*KEEP_V*/ false, PA, PW, /*WAVEFRONT*/ false>(ut, 12, d, nullptr);
+        // (WAVEFRONT = true is bit-identical — 104/104 parity tests — but measured SLOWER on B200, twice: PnP stage 8.0 ms
+        // against 6.4 ms per 256 pairs in round 1, and 42.9k against 52.2k stereo pairs/s with the two-launch solver (build
+        // with -DEPNP_WAVEFRONT=true): the six predicated chains cost more issue slots and address arithmetic than they hide)
+        jacobi_svd<12, 12, 12, /*KEEP_V*/ false, PA, PW, /*WAVEFRONT*/ EPNP_WAVEFRONT>(ut, 12, d, nullptr);
         for (int i = 0; i < 48; i++) ut8[i] = ut[96 + i];
     }
 
