@@ -494,22 +494,25 @@ struct EPnP {
         double l_6x10[60], rho[6];
         compute_L_6x10(ut8, l_6x10);
         compute_rho(rho);
-        double Betas[4][4], rep_errors[4], Rs[4][3][3], ts[4][3];
-        find_betas_approx_1(l_6x10, rho, Betas[1]);
-        gauss_newton(l_6x10, rho, Betas[1]);
-        rep_errors[1] = compute_R_and_t(ut8, Betas[1], Rs[1], ts[1]);
-        find_betas_approx_2(l_6x10, rho, Betas[2]);
-        gauss_newton(l_6x10, rho, Betas[2]);
-        rep_errors[2] = compute_R_and_t(ut8, Betas[2], Rs[2], ts[2]);
-        find_betas_approx_3(l_6x10, rho, Betas[3]);
-        gauss_newton(l_6x10, rho, Betas[3]);
-        rep_errors[3] = compute_R_and_t(ut8, Betas[3], Rs[3], ts[3]);
-        int N = 1;
-        if (rep_errors[2] < rep_errors[1]) N = 2;
-        if (rep_errors[3] < rep_errors[N]) N = 3;
-        for (int i = 0; i < 3; i++) {
-            t_out[i] = ts[N][i];
-            for (int j = 0; j < 3; j++) R_out[3 * i + j] = Rs[N][i][j];
+        // the three approximations share ONE copy of gauss_newton / compute_R_and_t (rolled loop: the second half of the
+        // solver stalled on instruction fetch as much as on its dependencies); the best is kept with OpenCV's strict
+        // comparisons: N = 1; if (err2 < err1) N = 2; if (err3 < err_N) N = 3
+        double best_err = 0;
+#pragma unroll 1
+        for (int a = 1; a <= 3; a++) {
+            double betas[4], R[3][3], t[3];
+            if (a == 1) find_betas_approx_1(l_6x10, rho, betas);
+            else if (a == 2) find_betas_approx_2(l_6x10, rho, betas);
+            else find_betas_approx_3(l_6x10, rho, betas);
+            gauss_newton(l_6x10, rho, betas);
+            const double err = compute_R_and_t(ut8, betas, R, t);
+            if (a == 1 || err < best_err) {
+                best_err = err;
+                for (int i = 0; i < 3; i++) {
+                    t_out[i] = t[i];
+                    for (int j = 0; j < 3; j++) R_out[3 * i + j] = R[i][j];
+                }
+            }
         }
     }
 
