@@ -26,9 +26,12 @@ CVM_HD void project_point_f32(const double* R, const double* t, const CamD& cam,
     const double r2 = x * x + y * y, r4 = r2 * r2, r6 = r4 * r2;
     const double a1 = 2 * x * y, a2 = r2 + 2 * x * x, a3 = r2 + 2 * y * y;
     const double cdist = 1 + cam.k[0] * r2 + cam.k[1] * r4 + cam.k[4] * r6;
-    const double icdist2 = 1. / (1 + 0. * r2 + 0. * r4 + 0. * r6);
-    const double xd0 = x * cdist * icdist2 + cam.k[2] * a1 + cam.k[3] * a2 + 0. * r2 + 0. * r4;
-    const double yd0 = y * cdist * icdist2 + cam.k[2] * a3 + cam.k[3] * a1 + 0. * r2 + 0. * r4;
+    // OpenCV also forms icdist2 = 1 / (1 + k4 r2 + k5 r4 + k6 r6) and adds s1 r2 + s2 r4 (+ s3, s4): with the reference's
+    // five coefficients (k4..k6 = s1..s4 = 0) that is 1 / 1 and + 0 for every finite point, so x * cdist * icdist2 + ... is
+    // x * cdist + ... bit for bit; a non-finite point projects to inf / NaN either way and fails the <= test either way.
+    // (The literal restatement cost a second fp64 division per evaluation: the scoring kernel's largest item.)
+    const double xd0 = x * cdist + cam.k[2] * a1 + cam.k[3] * a2;
+    const double yd0 = y * cdist + cam.k[2] * a3 + cam.k[3] * a1;
     u = (float)(xd0 * cam.fx + cam.cx);
     v = (float)(yd0 * cam.fy + cam.cy);
 }
